@@ -1,0 +1,243 @@
+// conv_kernels.cuh -- FP64 K x K clamp-to-edge stencil for sm_100a.
+//
+// Replaces apply_kernel_to_padded_point / apply_kernel_to_padded_image
+// (reference src/convolution/convolution-run.c:52-81) fused with update_borders
+// (src/convolution/convolution-util.c:281-294).
+//
+// Device image layout ("band"): rows of `dp` doubles; row of GLOBAL image row gr
+// sits at local row gr - row0 + halo; inside a row the inner pixel x is at
+// kLead + x (128-byte aligned), the reference's left pad columns at
+// [kLead-p, kLead), the right ones at [kLead+W, kLead+W+p).  `halo` rows above
+// and below the band hold the neighbouring ranks' edge rows (multi-GPU); at the
+// image's top/bottom the kernels clamp the row index instead, which is exactly
+// what the reference's aliased pad rows do (convolution-util.c:394-400).
+//
+// Exactness: val starts at +0.0 and every tap is one __dmul_rn followed by one
+// __dadd_rn in row-major tap order -- bit-identical to the reference (ISO C, no
+// contraction) for any finite data.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+
+namespace hgb {
+
+constexpr int kLead = 16;      // doubles in front of inner pixel 0 of every device row
+constexpr int kMaxTaps = 49;   // specialised kernels: 3x3, 5x5, 7x7
+
+struct Taps { double k[kMaxTaps]; };   // kernel parameter => constant bank operands
+
+struct BandGeom {
+    int W, H;        // inner image size (global)
+    int p;           // reference padding
+    int row0, rows;  // this band: global rows [row0, row0+rows)
+    int halo;        // halo rows stored above/below the band
+    int dp;          // device row pitch in doubles
+};
+
+__device__ __forceinline__ size_t band_row_off(const BandGeom &g, int gr) {
+    return (size_t)(gr - g.row0 + g.halo) * g.dp;
+}
+
+// ---- generic fallback: any kw, kh <= 2p+1 --------------------------------
+__global__ void __launch_bounds__(256)
+conv_generic_kernel(const double *__restrict__ in, double *__restrict__ out, BandGeom g,
+                    const double *__restrict__ taps, int kw, int kh) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = g.row0 + blockIdx.y;
+    if (x >= g.W) return;
+    double val = 0.0;
+    for (int ky = 0; ky < kh; ++ky) {
+        const int gr = min(max(y + ky - g.p, 0), g.H - 1);
+        const double *row = in + band_row_off(g, gr) + kLead - g.p + x;   // padded column x + kx
+        for (int kx = 0; kx < kw; ++kx) val = __dadd_rn(val, __dmul_rn(taps[ky * kw + kx], row[kx]));
+    }
+    double *orow = out + band_row_off(g, y) + kLead;
+    orow[x] = val;
+    if (x == 0)
+        for (int i = 1; i <= g.p; ++i) orow[-i] = val;            // update_borders, left
+    if (x == g.W - 1)
+        for (int i = 0; i < g.p; ++i) orow[g.W + i] = val;        // update_borders, right
+}
+
+// ---- mbarrier / bulk-copy (TMA engine) primitives -------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "@P1 bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// global -> shared bulk copy, completion counted on an mbarrier (SASS: UBLKCP)
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+            smem_u32(dst)),
+        "l"(src), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+
+// ---- specialised K x K (K = 2p+1) row-streaming kernel ---------------------
+// A CTA owns a strip of TW columns and a chunk of `chunk` output rows.  It
+// streams the chunk's input rows (chunk + 2p of them, row index clamped at the
+// image edge) through a shared-memory ring, K rows per stage, filled by bulk
+// copies issued by one thread and tracked with one mbarrier per stage.  Each
+// thread owns C adjacent columns and keeps K x C running sums in registers: input
+// row i feeds tap row ky of output row i - ky, so every output pixel receives
+// its taps in the reference's row-major order while each input value is read
+// from shared memory once per thread.
+template <int K, int TW, int C, int NST>
+struct ConvCfg {
+    static constexpr int P = K / 2;
+    static constexpr int LP = (P + 1) & ~1;          // halo columns staged per side (16 B granules)
+    static constexpr int ROWW = TW + 2 * LP;         // doubles per staged row
+    static constexpr int THREADS = TW / C;
+    static constexpr int STAGE_ROWS = K;
+    static constexpr size_t SMEM = (size_t)NST * STAGE_ROWS * ROWW * sizeof(double) + NST * 8;
+};
+
+template <int K, int TW, int C, int NST>
+__global__ void __launch_bounds__(TW / C)
+conv_stream_kernel(const double *__restrict__ in, double *__restrict__ out, BandGeom g, int chunk,
+                   const __grid_constant__ Taps taps) {
+    using Cfg = ConvCfg<K, TW, C, NST>;
+    constexpr int P = Cfg::P, LP = Cfg::LP, ROWW = Cfg::ROWW;
+    constexpr int NIN = C + 2 * P;                   // input values per thread per row
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    double *ring = reinterpret_cast<double *>(smem_raw);
+    uint64_t *full = reinterpret_cast<uint64_t *>(ring + (size_t)NST * K * ROWW);
+
+    const int x0 = blockIdx.x * TW;
+    const int y0 = g.row0 + blockIdx.y * chunk;                  // first output row (global)
+    const int nrows = min(chunk, g.row0 + g.rows - y0);          // output rows of this CTA
+    const int nin = nrows + 2 * P;                               // input rows streamed
+    const int nstages = (nin + K - 1) / K;
+    const int tid = threadIdx.x;
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < NST; ++s) mbar_init(&full[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    auto issue = [&](int st) {   // thread 0 only: fill ring slot st % NST with stage st
+        const int slot = st % NST;
+        const int i0 = st * K;
+        const int cnt = min(K, nin - i0);
+        mbar_expect_tx(&full[slot], (uint32_t)(cnt * ROWW * sizeof(double)));
+        for (int r = 0; r < cnt; ++r) {
+            const int gr = min(max(y0 - P + i0 + r, 0), g.H - 1);   // aliased pad rows == clamp
+            const double *src = in + band_row_off(g, gr) + kLead + x0 - LP;
+            bulk_g2s(ring + (size_t)(slot * K + r) * ROWW, src, ROWW * sizeof(double), &full[slot]);
+        }
+    };
+    if (tid == 0)
+        for (int st = 0; st < NST - 1 && st < nstages; ++st) issue(st);
+
+    double acc[K][C];
+#pragma unroll
+    for (int a = 0; a < K; ++a)
+#pragma unroll
+        for (int c = 0; c < C; ++c) acc[a][c] = 0.0;
+
+    const int xt = x0 + C * tid;                       // first column of this thread
+    const bool any_col = xt < g.W;
+
+    for (int st = 0; st < nstages; ++st) {
+        const int slot = st % NST;
+        // slot (st-1)%NST was drained by every thread before the barrier at the end of
+        // the previous iteration, so it can be refilled with stage st+NST-1 now
+        if (tid == 0 && st + NST - 1 < nstages) issue(st + NST - 1);
+        mbar_wait(&full[slot], (uint32_t)((st / NST) & 1));
+#pragma unroll
+        for (int ph = 0; ph < K; ++ph) {
+            const int i = st * K + ph;                 // input row index within the chunk
+            if (i < nin) {
+                const double *srow = ring + (size_t)(slot * K + ph) * ROWW + C * tid + (LP - P);
+                double v[NIN];
+#pragma unroll
+                for (int q = 0; q < NIN; ++q) v[q] = srow[q];
+#pragma unroll
+                for (int ky = 0; ky < K; ++ky) {
+                    const int a = (ph - ky + K) % K;   // compile-time accumulator slot of row i-ky
+#pragma unroll
+                    for (int c = 0; c < C; ++c) {
+                        double val = (ky == 0) ? 0.0 : acc[a][c];
+#pragma unroll
+                        for (int kx = 0; kx < K; ++kx)
+                            val = __dadd_rn(val, __dmul_rn(taps.k[ky * K + kx], v[c + kx]));
+                        acc[a][c] = val;
+                    }
+                    if (ky == K - 1 && i >= K - 1 && any_col) {      // output row i-(K-1) is complete
+                        const int gy = y0 + i - (K - 1);
+                        double *orow = out + band_row_off(g, gy) + kLead;
+                        if (C == 2 && xt + 1 < g.W) {
+                            *reinterpret_cast<double2 *>(orow + xt) = make_double2(acc[a][0], acc[a][1]);
+                        } else {
+#pragma unroll
+                            for (int c = 0; c < C; ++c)
+                                if (xt + c < g.W) orow[xt + c] = acc[a][c];
+                        }
+                        if (xt == 0) {                                // update_borders, left
+#pragma unroll
+                            for (int q = 1; q <= P; ++q) orow[-q] = acc[a][0];
+                        }
+#pragma unroll
+                        for (int c = 0; c < C; ++c)
+                            if (xt + c == g.W - 1) {                  // update_borders, right
+#pragma unroll
+                                for (int q = 0; q < P; ++q) orow[g.W + q] = acc[a][c];
+                            }
+                    }
+                }
+            }
+        }
+        __syncthreads();   // everyone is done reading this slot
+    }
+}
+
+// pad-column refresh for the rows a rank receives or for freshly uploaded data is
+// not needed: pad columns travel with the rows (full pitch) in every copy.
+
+// sequential row-major checksum (reference get_checksum, convolution-util.c:63-71):
+// one warp stages 32 doubles at a time, lane 0 adds them in order.  Exact but
+// serial; used by tests and the CLI path only.
+__global__ void __launch_bounds__(32)
+conv_checksum_seq_kernel(const double *__restrict__ img, BandGeom g, double carry_in,
+                         double *__restrict__ result) {
+    __shared__ double buf[2][1024];
+    double val = carry_in;
+    const int lane = threadIdx.x;
+    for (int y = g.row0; y < g.row0 + g.rows; ++y) {
+        const double *row = img + band_row_off(g, y) + kLead;
+        for (int x0 = 0; x0 < g.W; x0 += 1024) {
+            const int cnt = min(1024, g.W - x0);
+            double *b = buf[(x0 >> 10) & 1];
+            for (int q = lane; q < cnt; q += 32) b[q] = row[x0 + q];
+            __syncwarp();
+            if (lane == 0)
+                for (int q = 0; q < cnt; ++q) val = __dadd_rn(val, b[q]);
+            __syncwarp();
+        }
+    }
+    if (lane == 0) result[0] = val;
+}
+
+}  // namespace hgb

@@ -1,0 +1,415 @@
+// hgb_conv.cu -- host side of the convolution path: device-resident bands,
+// row-band sharding with halo exchange (ncclSend/ncclRecv or peer copies) and the
+// drop-in for run_on_padded_image() (reference src/convolution/convolution-run.c:41-49).
+#include "hgb_common.cuh"
+#include "conv_kernels.cuh"
+
+using namespace hgb;
+
+namespace {
+constexpr int kTW = 256;   // strip width of the streaming kernels
+
+struct CvShard {
+    DevCtx *dev = nullptr;
+    int index = 0;
+    int row0 = 0, rows = 0;
+    double *img[2] = {nullptr, nullptr};
+    double *taps_dev = nullptr;
+    double *scratch = nullptr;
+};
+}  // namespace
+
+struct hgb_conv {
+    int W = 0, H = 0, p = 0, world = 1, active = 1;  // active = ranks that own rows
+    bool rank_mode = false;
+    int dp = 0, halo = 0;
+    int kw = 0, kh = 0;
+    Taps taps;
+    std::vector<double> taps_host;
+    bool have_kernel = false;
+    int variant = 0, chunk = 0, exchange = HGB_EXCHANGE_NCCL;
+    int cur = 0;
+    bool uploaded = false;
+    std::vector<CvShard> sh;
+};
+
+static BandGeom geom(const hgb_conv *h, const CvShard &s) {
+    BandGeom g;
+    g.W = h->W; g.H = h->H; g.p = h->p;
+    g.row0 = s.row0; g.rows = s.rows;
+    g.halo = h->halo; g.dp = h->dp;
+    return g;
+}
+
+// band i of `active` equal bands (first H % active bands get one extra row)
+static void band_of(int H, int active, int i, int *row0, int *rows) {
+    if (i >= active) { *row0 = H; *rows = 0; return; }
+    int base = H / active, rem = H % active;
+    *row0 = i * base + (i < rem ? i : rem);
+    *rows = base + (i < rem ? 1 : 0);
+}
+
+static int cv_setup(hgb_conv *h) {
+    const int p = h->p;
+    h->halo = p;
+    // every band must be at least p rows tall so halos come from direct neighbours only
+    int act = h->world;
+    const int need = p > 0 ? p : 1;
+    if (act > h->H / need) act = h->H / need;
+    if (act < 1) act = 1;
+    h->active = act;
+    int wpad = (h->W + kTW - 1) / kTW * kTW;
+    h->dp = kLead + wpad + 16;            // staged strips may over-read up to LP columns
+    for (CvShard &s : h->sh) {
+        band_of(h->H, act, s.index, &s.row0, &s.rows);
+        HGB_CUDA(cudaSetDevice(s.dev->device));
+        const size_t bytes = (size_t)(s.rows + 2 * h->halo + 1) * h->dp * sizeof(double);
+        for (int b = 0; b < 2; ++b) {
+            HGB_CUDA(cudaMalloc(&s.img[b], bytes));
+            HGB_CUDA(cudaMemsetAsync(s.img[b], 0, bytes, s.dev->stream));
+        }
+        HGB_CUDA(cudaMalloc(&s.taps_dev, sizeof(double) * 1024));
+        HGB_CUDA(cudaMalloc(&s.scratch, 64));
+    }
+    return HGB_OK;
+}
+
+template <int K, int NST>
+static int launch_stream(const hgb_conv *h, const CvShard &s, const double *in, double *out) {
+    using Cfg = ConvCfg<K, kTW, 2, NST>;
+    auto kern = conv_stream_kernel<K, kTW, 2, NST>;
+    static bool attr_done[16] = {false};
+    if (!attr_done[s.dev->device & 15]) {
+        HGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
+        attr_done[s.dev->device & 15] = true;
+    }
+    int chunk = h->chunk > 0 ? h->chunk : 128;
+    if (chunk > s.rows) chunk = s.rows;
+    dim3 grid((h->W + kTW - 1) / kTW, (s.rows + chunk - 1) / chunk);
+    kern<<<grid, Cfg::THREADS, Cfg::SMEM, s.dev->stream>>>(in, out, geom(h, s), chunk, h->taps);
+    HGB_LAUNCHED();
+    return HGB_OK;
+}
+
+static int launch_conv(const hgb_conv *h, const CvShard &s, const double *in, double *out) {
+    if (s.rows <= 0) return HGB_OK;
+    const bool square = h->kw == h->kh && h->kw == 2 * h->p + 1;
+    if (h->variant != 1 && square) {
+        if (h->kw == 3) return launch_stream<3, 4>(h, s, in, out);
+        if (h->kw == 5) return launch_stream<5, 3>(h, s, in, out);
+        if (h->kw == 7) return launch_stream<7, 3>(h, s, in, out);
+    }
+    dim3 grid((h->W + 255) / 256, s.rows);
+    conv_generic_kernel<<<grid, 256, 0, s.dev->stream>>>(in, out, geom(h, s), s.taps_dev, h->kw, h->kh);
+    HGB_LAUNCHED();
+    return HGB_OK;
+}
+
+// exchange the p edge rows of state `b` between neighbouring bands
+static int halo_exchange(hgb_conv *h, int b) {
+    if (h->active <= 1 || h->p == 0) return HGB_OK;
+    const size_t cnt = (size_t)h->p * h->dp;     // p full device rows (pad columns included)
+    if (!h->rank_mode && h->exchange == HGB_EXCHANGE_P2P) {
+        // peer copies on the RECEIVER's stream after the sender's kernel finished
+        for (CvShard &s : h->sh) {
+            HGB_CUDA(cudaSetDevice(s.dev->device));
+            HGB_CUDA(cudaEventRecord(s.dev->ev_step, s.dev->stream));
+        }
+        for (CvShard &s : h->sh) {
+            if (s.rows <= 0) continue;
+            HGB_CUDA(cudaSetDevice(s.dev->device));
+            if (s.index > 0) {
+                CvShard &up = h->sh[s.index - 1];
+                HGB_CUDA(cudaStreamWaitEvent(s.dev->stream, up.dev->ev_step, 0));
+                HGB_CUDA(cudaMemcpyPeerAsync(s.img[b], s.dev->device,
+                                             up.img[b] + (size_t)up.rows * h->dp, up.dev->device,
+                                             cnt * sizeof(double), s.dev->stream));
+            }
+            if (s.index < h->active - 1) {
+                CvShard &dn = h->sh[s.index + 1];
+                HGB_CUDA(cudaStreamWaitEvent(s.dev->stream, dn.dev->ev_step, 0));
+                HGB_CUDA(cudaMemcpyPeerAsync(s.img[b] + (size_t)(h->halo + s.rows) * h->dp,
+                                             s.dev->device, dn.img[b] + (size_t)h->halo * h->dp,
+                                             dn.dev->device, cnt * sizeof(double), s.dev->stream));
+            }
+        }
+        // a band may only be overwritten (next iteration writes the OTHER buffer, but the
+        // one after that writes this one) once its neighbours have pulled their halos
+        for (CvShard &s : h->sh) {
+            HGB_CUDA(cudaSetDevice(s.dev->device));
+            HGB_CUDA(cudaEventRecord(s.dev->ev_step, s.dev->stream));
+        }
+        for (CvShard &s : h->sh)
+            for (int d = -1; d <= 1; d += 2) {
+                int o = s.index + d;
+                if (o < 0 || o >= h->active) continue;
+                HGB_CUDA(cudaStreamWaitEvent(s.dev->stream, h->sh[o].dev->ev_step, 0));
+            }
+        return HGB_OK;
+    }
+    HGB_NCCL(nccl().GroupStart());
+    for (CvShard &s : h->sh) {
+        if (s.rows <= 0) continue;
+        ncclComm_t comm = h->rank_mode ? rt().rank_comm : s.dev->comm;
+        double *base = s.img[b];
+        if (s.index > 0) {
+            HGB_NCCL(nccl().Send(base + (size_t)h->halo * h->dp, cnt, ncclDouble, s.index - 1, comm,
+                                 s.dev->stream));
+            HGB_NCCL(nccl().Recv(base, cnt, ncclDouble, s.index - 1, comm, s.dev->stream));
+        }
+        if (s.index < h->active - 1) {
+            HGB_NCCL(nccl().Send(base + (size_t)s.rows * h->dp, cnt, ncclDouble, s.index + 1, comm,
+                                 s.dev->stream));
+            HGB_NCCL(nccl().Recv(base + (size_t)(h->halo + s.rows) * h->dp, cnt, ncclDouble,
+                                 s.index + 1, comm, s.dev->stream));
+        }
+    }
+    HGB_NCCL(nccl().GroupEnd());
+    return HGB_OK;
+}
+
+extern "C" {
+
+int hgb_conv_destroy(hgb_conv *h) {
+    if (!h) return HGB_OK;
+    for (CvShard &s : h->sh) {
+        cudaSetDevice(s.dev->device);
+        cudaStreamSynchronize(s.dev->stream);
+        cudaFree(s.img[0]);
+        cudaFree(s.img[1]);
+        cudaFree(s.taps_dev);
+        cudaFree(s.scratch);
+    }
+    delete h;
+    return HGB_OK;
+}
+
+static int cv_check_dims(int w, int hh, int p) {
+    HGB_ARG(w > 0 && hh > 0, "image size must be positive");
+    HGB_ARG(p >= 0 && p <= kLead - 4, "padding must be in [0, 12]");
+    return HGB_OK;
+}
+
+int hgb_conv_create(hgb_conv **out, int inner_w, int inner_h, int padding, int ngpus) {
+    HGB_ARG(out, "out == NULL");
+    HGB_TRY(cv_check_dims(inner_w, inner_h, padding));
+    int g = 1;
+    HGB_TRY(resolve_ngpus(ngpus, &g));
+    HGB_TRY(ensure_devices(g));
+    hgb_conv *h = new hgb_conv();
+    h->W = inner_w; h->H = inner_h; h->p = padding; h->world = g;
+    h->sh.resize(g);
+    for (int i = 0; i < g; ++i) { h->sh[i].dev = &rt().devs[i]; h->sh[i].index = i; }
+    int rc = cv_setup(h);
+    if (rc != HGB_OK) { hgb_conv_destroy(h); return rc; }
+    *out = h;
+    return HGB_OK;
+}
+
+int hgb_conv_create_rank(hgb_conv **out, int inner_w, int inner_h, int padding) {
+    HGB_ARG(out, "out == NULL");
+    HGB_TRY(cv_check_dims(inner_w, inner_h, padding));
+    Runtime &r = rt();
+    HGB_TRY(ensure_rank_dev());
+    if (r.world > 1 && !r.rank_comm) {
+        set_error("hgb_comm_init_rank must be called before hgb_conv_create_rank");
+        return HGB_ERR_STATE;
+    }
+    hgb_conv *h = new hgb_conv();
+    h->W = inner_w; h->H = inner_h; h->p = padding; h->world = r.world; h->rank_mode = true;
+    h->sh.resize(1);
+    h->sh[0].dev = &r.rank_dev;
+    h->sh[0].index = r.rank;
+    int rc = cv_setup(h);
+    if (rc != HGB_OK) { hgb_conv_destroy(h); return rc; }
+    *out = h;
+    return HGB_OK;
+}
+
+int hgb_conv_set_kernel(hgb_conv *h, const double *kernel, int kw, int kh) {
+    HGB_ARG(h && kernel, "handle / kernel");
+    HGB_ARG(kw >= 1 && kh >= 1, "kernel size must be positive");
+    // the reference reads image[y+ky-p][x+kx-p]; larger kernels index outside its rows
+    HGB_ARG(kw <= 2 * h->p + 1 && kh <= 2 * h->p + 1, "kernel larger than 2*padding+1");
+    h->kw = kw; h->kh = kh;
+    h->taps_host.assign(kernel, kernel + (size_t)kw * kh);
+    memset(&h->taps, 0, sizeof(h->taps));
+    if ((size_t)kw * kh <= (size_t)kMaxTaps) memcpy(h->taps.k, kernel, sizeof(double) * kw * kh);
+    for (CvShard &s : h->sh) {
+        HGB_CUDA(cudaSetDevice(s.dev->device));
+        HGB_CUDA(cudaMemcpyAsync(s.taps_dev, h->taps_host.data(), sizeof(double) * kw * kh,
+                                 cudaMemcpyHostToDevice, s.dev->stream));
+        HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
+    }
+    h->have_kernel = true;
+    return HGB_OK;
+}
+
+int hgb_conv_tune(hgb_conv *h, int variant, int band_rows) {
+    HGB_ARG(h && variant >= 0 && variant <= 1 && band_rows >= 0, "handle / variant / band_rows");
+    h->variant = variant;
+    h->chunk = band_rows;
+    return HGB_OK;
+}
+
+int hgb_conv_set_exchange(hgb_conv *h, int kind) {
+    HGB_ARG(h && (kind == HGB_EXCHANGE_NCCL || kind == HGB_EXCHANGE_P2P), "handle / kind");
+    if (kind == HGB_EXCHANGE_P2P && h->world > 1) {
+        if (h->rank_mode) { set_error("peer exchange needs the single-process handle"); return HGB_ERR_STATE; }
+        HGB_TRY(ensure_peer_access(h->world));
+    }
+    h->exchange = kind;
+    return HGB_OK;
+}
+
+int hgb_conv_band(hgb_conv *h, int *row0, int *rows) {
+    HGB_ARG(h && row0 && rows, "handle / out pointers");
+    if (h->rank_mode) { *row0 = h->sh[0].row0; *rows = h->sh[0].rows; }
+    else { *row0 = 0; *rows = h->H; }
+    return HGB_OK;
+}
+
+// Host rows: pitch W+2p.  Single-process handle: `cur` is the whole image.  Rank
+// handle: `cur` is this rank's band only (rows [row0,row0+rows)); halos are filled
+// by an exchange.
+int hgb_conv_upload(hgb_conv *h, const double *cur) {
+    HGB_ARG(h && cur, "handle / image");
+    const size_t hp = (size_t)h->W + 2 * h->p;
+    for (CvShard &s : h->sh) {
+        if (s.rows <= 0) continue;
+        HGB_CUDA(cudaSetDevice(s.dev->device));
+        int g0 = s.row0, g1 = s.row0 + s.rows;
+        const double *src = cur;
+        if (!h->rank_mode) {   // halos straight from the host image
+            g0 = max(0, s.row0 - h->halo);
+            g1 = min(h->H, s.row0 + s.rows + h->halo);
+            src = cur + (size_t)g0 * hp;
+        }
+        double *dst = s.img[0] + (size_t)(g0 - s.row0 + h->halo) * h->dp + kLead - h->p;
+        HGB_CUDA(cudaMemcpy2DAsync(dst, h->dp * sizeof(double), src, hp * sizeof(double),
+                                   hp * sizeof(double), g1 - g0, cudaMemcpyHostToDevice,
+                                   s.dev->stream));
+    }
+    h->cur = 0;
+    h->uploaded = true;
+    if (h->rank_mode && h->world > 1) HGB_TRY(halo_exchange(h, 0));
+    for (CvShard &s : h->sh) HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
+    return HGB_OK;
+}
+
+int hgb_conv_step(hgb_conv *h, int iterations, float *ms) {
+    HGB_ARG(h && iterations >= 0, "handle / iterations");
+    if (!h->uploaded || !h->have_kernel) {
+        set_error("hgb_conv_step needs hgb_conv_upload and hgb_conv_set_kernel first");
+        return HGB_ERR_STATE;
+    }
+    if (h->active > 1 && !h->rank_mode && h->exchange == HGB_EXCHANGE_NCCL)
+        HGB_TRY(ensure_sp_comm(h->world));
+    for (CvShard &s : h->sh) {
+        HGB_CUDA(cudaSetDevice(s.dev->device));
+        HGB_CUDA(cudaEventRecord(s.dev->ev_begin, s.dev->stream));
+    }
+    for (int it = 0; it < iterations; ++it) {
+        const int cur = h->cur, nxt = cur ^ 1;
+        for (CvShard &s : h->sh) {
+            HGB_CUDA(cudaSetDevice(s.dev->device));
+            HGB_TRY(launch_conv(h, s, s.img[cur], s.img[nxt]));
+        }
+        HGB_TRY(halo_exchange(h, nxt));
+        h->cur = nxt;
+    }
+    float worst = 0.f;
+    for (CvShard &s : h->sh) {
+        HGB_CUDA(cudaSetDevice(s.dev->device));
+        HGB_CUDA(cudaEventRecord(s.dev->ev_end, s.dev->stream));
+    }
+    for (CvShard &s : h->sh) {
+        HGB_CUDA(cudaEventSynchronize(s.dev->ev_end));
+        float t = 0.f;
+        HGB_CUDA(cudaEventElapsedTime(&t, s.dev->ev_begin, s.dev->ev_end));
+        worst = t > worst ? t : worst;
+    }
+    HGB_CUDA(cudaGetLastError());
+    if (ms) *ms = worst;
+    return HGB_OK;
+}
+
+int hgb_conv_download(hgb_conv *h, double *cur, double *prev) {
+    HGB_ARG(h, "handle");
+    if (!h->uploaded) { set_error("hgb_conv_download before upload"); return HGB_ERR_STATE; }
+    const size_t hp = (size_t)h->W + 2 * h->p;
+    double *dsts[2] = {cur, prev};
+    for (int w = 0; w < 2; ++w) {
+        if (!dsts[w]) continue;
+        const int b = w == 0 ? h->cur : h->cur ^ 1;
+        for (CvShard &s : h->sh) {
+            if (s.rows <= 0) continue;
+            HGB_CUDA(cudaSetDevice(s.dev->device));
+            double *dst = dsts[w] + (h->rank_mode ? 0 : (size_t)s.row0 * hp);
+            const double *src = s.img[b] + (size_t)h->halo * h->dp + kLead - h->p;
+            HGB_CUDA(cudaMemcpy2DAsync(dst, hp * sizeof(double), src, h->dp * sizeof(double),
+                                       hp * sizeof(double), s.rows, cudaMemcpyDeviceToHost,
+                                       s.dev->stream));
+        }
+    }
+    for (CvShard &s : h->sh) HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
+    return HGB_OK;
+}
+
+int hgb_conv_checksum(hgb_conv *h, double *checksum) {
+    HGB_ARG(h && checksum, "handle / checksum");
+    if (!h->uploaded) { set_error("checksum before upload"); return HGB_ERR_STATE; }
+    if (h->rank_mode && h->world > 1) {
+        set_error("sequential checksum is only available on the single-process handle");
+        return HGB_ERR_STATE;
+    }
+    double carry = 0.0;   // the sum is sequential: bands are chained in row order
+    for (CvShard &s : h->sh) {
+        if (s.rows <= 0) continue;
+        HGB_CUDA(cudaSetDevice(s.dev->device));
+        conv_checksum_seq_kernel<<<1, 32, 0, s.dev->stream>>>(s.img[h->cur], geom(h, s), carry, s.scratch);
+        HGB_LAUNCHED();
+        HGB_CUDA(cudaMemcpyAsync(&carry, s.scratch, sizeof(double), cudaMemcpyDeviceToHost, s.dev->stream));
+        HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
+    }
+    *checksum = carry;
+    return HGB_OK;
+}
+
+// ---- the drop-in ---------------------------------------------------------
+static hgb_conv *g_cv = nullptr;
+static int g_cv_key[4] = {0, 0, 0, 0};
+static int g_cv_exchange = HGB_EXCHANGE_NCCL;
+
+int hgb_conv_run(double *cur, double *prev, int inner_w, int inner_h, int padding,
+                 const double *kernel, int kw, int kh, int iterations, int ngpus) {
+    HGB_ARG(iterations >= 0, "negative iteration count");
+    int g = 1;
+    HGB_TRY(resolve_ngpus(ngpus, &g));          // fails loudly without a GPU
+    HGB_TRY(cv_check_dims(inner_w, inner_h, padding));
+    HGB_ARG(kernel && kw >= 1 && kh >= 1, "kernel");
+    HGB_ARG(kw <= 2 * padding + 1 && kh <= 2 * padding + 1, "kernel larger than 2*padding+1");
+    if (iterations == 0) return HGB_OK;         // the reference's loop body never runs
+    HGB_ARG(cur && prev, "NULL image");
+    if (!g_cv || g_cv_key[0] != inner_w || g_cv_key[1] != inner_h || g_cv_key[2] != padding ||
+        g_cv_key[3] != g) {
+        hgb_conv_destroy(g_cv);
+        g_cv = nullptr;
+        HGB_TRY(hgb_conv_create(&g_cv, inner_w, inner_h, padding, g));
+        g_cv_key[0] = inner_w; g_cv_key[1] = inner_h; g_cv_key[2] = padding; g_cv_key[3] = g;
+    }
+    HGB_TRY(hgb_conv_set_exchange(g_cv, g_cv_exchange));
+    HGB_TRY(hgb_conv_set_kernel(g_cv, kernel, kw, kh));
+    HGB_TRY(hgb_conv_upload(g_cv, cur));
+    HGB_TRY(hgb_conv_step(g_cv, iterations, nullptr));
+    return hgb_conv_download(g_cv, cur, prev);
+}
+
+}  // extern "C"
+
+namespace hgb {
+void conv_drop_cache() {
+    hgb_conv_destroy(g_cv);
+    g_cv = nullptr;
+}
+}  // namespace hgb

@@ -1,0 +1,457 @@
+// hgb_nbody.cu -- host side of the nbody path: device-resident handle, target
+// sharding, position exchange (ncclAllGather or fused peer stores) and the
+// drop-in for the reference's run() (src/nbody/nbody-run.c:27-37).
+#include "hgb_common.cuh"
+#include "nbody_kernels.cuh"
+
+using namespace hgb;
+
+namespace {
+constexpr int kAlign = 1024;  // >= largest TILE (256 threads x 4 loads)
+
+struct NbShard {
+    DevCtx *dev = nullptr;
+    int index = 0;               // which target slice this device owns
+    double *state[2] = {nullptr, nullptr};  // ping-pong SoA, 3*npad doubles each
+    double *stage = nullptr;     // AoS staging, 3*npad doubles
+    double *partials = nullptr;  // energy block sums
+    int *tlist = nullptr;
+    int tlist_cap = 0;
+};
+}  // namespace
+
+struct hgb_nbody {
+    int n = 0, npad = 0, slice = 0, world = 1;
+    bool rank_mode = false;
+    int mode = HGB_NBODY_EXACT, exchange = HGB_EXCHANGE_NCCL;
+    int block = 0, unroll = 0;
+    int cur = 0;  // state[cur] holds the newest positions
+    bool uploaded = false;
+    std::vector<NbShard> sh;
+};
+
+static int g_default_mode = HGB_NBODY_EXACT;
+static int g_default_exchange = HGB_EXCHANGE_NCCL;
+
+template <int BLOCK, int UNROLL>
+static void launch_variant(bool fast, int grid, cudaStream_t st, const double *src, int npad, int n,
+                           int t0, int count, const int *tlist, const PeerOut &out, double *out_list) {
+    if (fast)
+        nbody_step_kernel<BLOCK, UNROLL, true><<<grid, BLOCK, 0, st>>>(src, npad, n, t0, count, tlist,
+                                                                     out, out_list);
+    else
+        nbody_step_kernel<BLOCK, UNROLL, false><<<grid, BLOCK, 0, st>>>(src, npad, n, t0, count, tlist,
+                                                                      out, out_list);
+}
+
+static int launch_step(const hgb_nbody *h, const NbShard &s, const double *src, int t0, int count,
+                       const int *tlist, const PeerOut &out, double *out_list) {
+    if (count <= 0) return HGB_OK;
+    const bool fast = h->mode == HGB_NBODY_FAST;
+    int block = h->block ? h->block : 128;
+    int unroll = h->unroll ? h->unroll : 2;
+    const int grid = (count + block - 1) / block;
+    cudaStream_t st = s.dev->stream;
+#define HGB_V(B, U)                                                                             \
+    if (block == B && unroll == U) {                                                            \
+        launch_variant<B, U>(fast, grid, st, src, h->npad, h->n, t0, count, tlist, out, out_list); \
+        HGB_LAUNCHED();                                                                         \
+        return HGB_OK;                                                                          \
+    }
+    HGB_V(64, 1) HGB_V(64, 2) HGB_V(64, 4)
+    HGB_V(128, 1) HGB_V(128, 2) HGB_V(128, 4)
+    HGB_V(256, 1) HGB_V(256, 2) HGB_V(256, 4)
+#undef HGB_V
+    set_error("no nbody kernel variant block=%d unroll=%d", block, unroll);
+    return HGB_ERR_ARG;
+}
+
+static int nb_alloc(hgb_nbody *h) {
+    for (NbShard &s : h->sh) {
+        HGB_CUDA(cudaSetDevice(s.dev->device));
+        const size_t bytes = 3ull * h->npad * sizeof(double);
+        for (int b = 0; b < 2; ++b) {
+            HGB_CUDA(cudaMalloc(&s.state[b], bytes));
+            HGB_CUDA(cudaMemsetAsync(s.state[b], 0, bytes, s.dev->stream));
+        }
+        HGB_CUDA(cudaMalloc(&s.stage, bytes));
+        HGB_CUDA(cudaMalloc(&s.partials, sizeof(double) * (h->slice / 64 + 2)));
+    }
+    return HGB_OK;
+}
+
+extern "C" {
+
+int hgb_set_nbody_mode(int mode) {
+    HGB_ARG(mode == HGB_NBODY_EXACT || mode == HGB_NBODY_FAST, "mode");
+    g_default_mode = mode;
+    return HGB_OK;
+}
+
+int hgb_set_exchange(int kind) {
+    HGB_ARG(kind == HGB_EXCHANGE_NCCL || kind == HGB_EXCHANGE_P2P, "exchange kind");
+    g_default_exchange = kind;
+    return HGB_OK;
+}
+
+int hgb_nbody_destroy(hgb_nbody *h) {
+    if (!h) return HGB_OK;
+    for (NbShard &s : h->sh) {
+        cudaSetDevice(s.dev->device);
+        cudaStreamSynchronize(s.dev->stream);
+        cudaFree(s.state[0]);
+        cudaFree(s.state[1]);
+        cudaFree(s.stage);
+        cudaFree(s.partials);
+        if (s.tlist) cudaFree(s.tlist);
+    }
+    delete h;
+    return HGB_OK;
+}
+
+int hgb_nbody_create(hgb_nbody **out, int n, int ngpus) {
+    HGB_ARG(out && n > 0, "out == NULL or n <= 0");
+    int g = 1;
+    HGB_TRY(resolve_ngpus(ngpus, &g));
+    HGB_ARG(g <= kMaxPeers, "more than 8 GPUs");
+    HGB_TRY(ensure_devices(g));
+    hgb_nbody *h = new hgb_nbody();
+    h->n = n;
+    h->world = g;
+    h->slice = shard_size(n, g, kAlign);
+    h->npad = h->slice * g;
+    h->mode = g_default_mode;
+    h->exchange = g_default_exchange;
+    h->sh.resize(g);
+    for (int i = 0; i < g; ++i) {
+        h->sh[i].dev = &rt().devs[i];
+        h->sh[i].index = i;
+    }
+    int rc = nb_alloc(h);
+    if (rc != HGB_OK) { hgb_nbody_destroy(h); return rc; }
+    *out = h;
+    return HGB_OK;
+}
+
+int hgb_nbody_create_rank(hgb_nbody **out, int n) {
+    HGB_ARG(out && n > 0, "out == NULL or n <= 0");
+    Runtime &r = rt();
+    HGB_TRY(ensure_rank_dev());
+    if (r.world > 1 && !r.rank_comm) {
+        set_error("hgb_comm_init_rank must be called before hgb_nbody_create_rank");
+        return HGB_ERR_STATE;
+    }
+    hgb_nbody *h = new hgb_nbody();
+    h->n = n;
+    h->world = r.world;
+    h->rank_mode = true;
+    h->slice = shard_size(n, r.world, kAlign);
+    h->npad = h->slice * r.world;
+    h->mode = g_default_mode;
+    h->exchange = HGB_EXCHANGE_NCCL;
+    h->sh.resize(1);
+    h->sh[0].dev = &r.rank_dev;
+    h->sh[0].index = r.rank;
+    int rc = nb_alloc(h);
+    if (rc != HGB_OK) { hgb_nbody_destroy(h); return rc; }
+    *out = h;
+    return HGB_OK;
+}
+
+int hgb_nbody_config(hgb_nbody *h, int mode, int exchange) {
+    HGB_ARG(h, "handle");
+    HGB_ARG(mode == HGB_NBODY_EXACT || mode == HGB_NBODY_FAST, "mode");
+    HGB_ARG(exchange == HGB_EXCHANGE_NCCL || exchange == HGB_EXCHANGE_P2P, "exchange");
+    if (exchange == HGB_EXCHANGE_P2P && h->world > 1) {
+        if (h->rank_mode) {
+            set_error("peer-store exchange needs the single-process multi-GPU handle");
+            return HGB_ERR_STATE;
+        }
+        HGB_TRY(ensure_peer_access(h->world));
+    }
+    h->mode = mode;
+    h->exchange = exchange;
+    return HGB_OK;
+}
+
+int hgb_nbody_tune(hgb_nbody *h, int block, int unroll) {
+    HGB_ARG(h, "handle");
+    HGB_ARG(block == 0 || block == 64 || block == 128 || block == 256, "block in {64,128,256}");
+    HGB_ARG(unroll == 0 || unroll == 1 || unroll == 2 || unroll == 4, "unroll in {1,2,4}");
+    h->block = block;
+    h->unroll = unroll;
+    return HGB_OK;
+}
+
+int hgb_nbody_upload(hgb_nbody *h, const double *pos_aos) {
+    HGB_ARG(h && pos_aos, "handle / positions");
+    for (NbShard &s : h->sh) {
+        HGB_CUDA(cudaSetDevice(s.dev->device));
+        HGB_CUDA(cudaMemcpyAsync(s.stage, pos_aos, 3ull * h->n * sizeof(double),
+                                 cudaMemcpyHostToDevice, s.dev->stream));
+        aos_to_soa_kernel<<<(h->npad + 255) / 256, 256, 0, s.dev->stream>>>(s.stage, s.state[0],
+                                                                            h->n, h->npad);
+        HGB_LAUNCHED();
+    }
+    for (NbShard &s : h->sh) HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
+    h->cur = 0;
+    h->uploaded = true;
+    return HGB_OK;
+}
+
+int hgb_nbody_step(hgb_nbody *h, int iterations, float *ms) {
+    HGB_ARG(h && iterations >= 0, "handle / iterations");
+    if (!h->uploaded) { set_error("hgb_nbody_step before hgb_nbody_upload"); return HGB_ERR_STATE; }
+    const bool multi = h->world > 1;
+    const bool p2p = multi && h->exchange == HGB_EXCHANGE_P2P;
+    if (multi && !p2p && !h->rank_mode) HGB_TRY(ensure_sp_comm(h->world));
+    for (NbShard &s : h->sh) {
+        HGB_CUDA(cudaSetDevice(s.dev->device));
+        HGB_CUDA(cudaEventRecord(s.dev->ev_begin, s.dev->stream));
+    }
+    for (int it = 0; it < iterations; ++it) {
+        const int cur = h->cur, nxt = cur ^ 1;
+        for (NbShard &s : h->sh) {
+            HGB_CUDA(cudaSetDevice(s.dev->device));
+            PeerOut out;
+            out.count = 1;
+            out.base[0] = s.state[nxt];
+            if (p2p) {
+                out.count = h->world;
+                for (int p = 0; p < h->world; ++p) out.base[p] = h->sh[p].state[nxt];
+            }
+            const int t0 = s.index * h->slice;
+            const int count = max(0, min(h->n, t0 + h->slice) - t0);
+            HGB_TRY(launch_step(h, s, s.state[cur], t0, count, nullptr, out, nullptr));
+        }
+        if (p2p) {
+            // every device's next step reads what all peers stored: join the streams
+            for (NbShard &s : h->sh) {
+                HGB_CUDA(cudaSetDevice(s.dev->device));
+                HGB_CUDA(cudaEventRecord(s.dev->ev_step, s.dev->stream));
+            }
+            for (NbShard &s : h->sh)
+                for (NbShard &o : h->sh)
+                    if (&o != &s) HGB_CUDA(cudaStreamWaitEvent(s.dev->stream, o.dev->ev_step, 0));
+        } else if (multi) {
+            HGB_NCCL(nccl().GroupStart());
+            for (NbShard &s : h->sh) {
+                ncclComm_t comm = h->rank_mode ? rt().rank_comm : s.dev->comm;
+                for (int c = 0; c < 3; ++c) {
+                    double *recv = s.state[nxt] + (size_t)c * h->npad;
+                    HGB_NCCL(nccl().AllGather(recv + (size_t)s.index * h->slice, recv, h->slice,
+                                              ncclDouble, comm, s.dev->stream));
+                }
+            }
+            HGB_NCCL(nccl().GroupEnd());
+        }
+        h->cur = nxt;
+    }
+    for (NbShard &s : h->sh) {
+        HGB_CUDA(cudaSetDevice(s.dev->device));
+        HGB_CUDA(cudaEventRecord(s.dev->ev_end, s.dev->stream));
+    }
+    float worst = 0.f;
+    for (NbShard &s : h->sh) {
+        HGB_CUDA(cudaEventSynchronize(s.dev->ev_end));
+        float t = 0.f;
+        HGB_CUDA(cudaEventElapsedTime(&t, s.dev->ev_begin, s.dev->ev_end));
+        worst = t > worst ? t : worst;
+    }
+    HGB_CUDA(cudaGetLastError());
+    if (ms) *ms = worst;
+    return HGB_OK;
+}
+
+int hgb_nbody_download(hgb_nbody *h, double *cur_aos, double *prev_aos) {
+    HGB_ARG(h, "handle");
+    if (!h->uploaded) { set_error("hgb_nbody_download before upload"); return HGB_ERR_STATE; }
+    NbShard &s = h->sh[0];  // after the exchange every shard holds all n bodies
+    HGB_CUDA(cudaSetDevice(s.dev->device));
+    double *dst[2] = {cur_aos, prev_aos};
+    for (int w = 0; w < 2; ++w) {
+        if (!dst[w]) continue;
+        soa_to_aos_kernel<<<(h->n + 255) / 256, 256, 0, s.dev->stream>>>(
+            s.state[w == 0 ? h->cur : h->cur ^ 1], s.stage, h->n, h->npad);
+        HGB_LAUNCHED();
+        HGB_CUDA(cudaMemcpyAsync(dst[w], s.stage, 3ull * h->n * sizeof(double),
+                                 cudaMemcpyDeviceToHost, s.dev->stream));
+        HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
+    }
+    return HGB_OK;
+}
+
+int hgb_nbody_accel_subset(hgb_nbody *h, const int *targets, int count, double *out_aos) {
+    HGB_ARG(h && targets && out_aos && count >= 0, "handle / targets / out");
+    if (!h->uploaded) { set_error("accel_subset before upload"); return HGB_ERR_STATE; }
+    if (count == 0) return HGB_OK;
+    HGB_ARG(3ll * count <= 3ll * h->npad, "count larger than the body set");
+    for (int i = 0; i < count; ++i) HGB_ARG(targets[i] >= 0 && targets[i] < h->n, "target index");
+    NbShard &s = h->sh[0];
+    HGB_CUDA(cudaSetDevice(s.dev->device));
+    if (s.tlist_cap < count) {
+        if (s.tlist) cudaFree(s.tlist);
+        HGB_CUDA(cudaMalloc(&s.tlist, sizeof(int) * count));
+        s.tlist_cap = count;
+    }
+    HGB_CUDA(cudaMemcpyAsync(s.tlist, targets, sizeof(int) * count, cudaMemcpyHostToDevice,
+                             s.dev->stream));
+    PeerOut out;
+    out.count = 0;
+    HGB_TRY(launch_step(h, s, s.state[h->cur], 0, count, s.tlist, out, s.stage));
+    HGB_CUDA(cudaMemcpyAsync(out_aos, s.stage, 3ull * count * sizeof(double), cudaMemcpyDeviceToHost,
+                             s.dev->stream));
+    HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
+    return HGB_OK;
+}
+
+int hgb_nbody_energy(hgb_nbody *h, double *energy) {
+    HGB_ARG(h && energy, "handle / energy");
+    if (!h->uploaded) { set_error("energy before upload"); return HGB_ERR_STATE; }
+    double total = 0.0;
+    std::vector<double> part(h->sh.size(), 0.0);
+    for (size_t i = 0; i < h->sh.size(); ++i) {
+        NbShard &s = h->sh[i];
+        HGB_CUDA(cudaSetDevice(s.dev->device));
+        const int t0 = s.index * h->slice;
+        const int count = max(0, min(h->n, t0 + h->slice) - t0);
+        if (count == 0) continue;
+        const int grid = (count + 127) / 128;
+        nbody_energy_kernel<128><<<grid, 128, 0, s.dev->stream>>>(s.state[h->cur], h->npad, h->n, t0,
+                                                                 count, s.partials + 1);
+        HGB_LAUNCHED();
+        sum_partials_kernel<<<1, 256, 0, s.dev->stream>>>(s.partials + 1, grid, s.partials);
+        HGB_LAUNCHED();
+        if (h->rank_mode && h->world > 1)
+            HGB_NCCL(nccl().AllReduce(s.partials, s.partials, 1, ncclDouble, ncclSum, rt().rank_comm,
+                                      s.dev->stream));
+        HGB_CUDA(cudaMemcpyAsync(&part[i], s.partials, sizeof(double), cudaMemcpyDeviceToHost,
+                                 s.dev->stream));
+    }
+    for (NbShard &s : h->sh) HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
+    for (double p : part) total += p;
+    *energy = -kG * 0.5 * total;  // every pair was counted twice
+    return HGB_OK;
+}
+
+// ---- the drop-in ---------------------------------------------------------
+static hgb_nbody *g_cached = nullptr;
+static int g_cached_n = 0, g_cached_g = 0;
+
+int hgb_nbody_run(double *planets_aos, double *buffer_aos, int n, int iterations, int ngpus) {
+    HGB_ARG(n >= 0 && iterations >= 0, "negative size or iteration count");
+    int g = 1;
+    HGB_TRY(resolve_ngpus(ngpus, &g));            // fails loudly without a GPU, even for n == 0
+    if (n == 0 || iterations == 0) return HGB_OK; // the reference's loops do nothing either
+    HGB_ARG(planets_aos && buffer_aos, "NULL body array");
+    if (!g_cached || g_cached_n != n || g_cached_g != g) {
+        hgb_nbody_destroy(g_cached);
+        g_cached = nullptr;
+        HGB_TRY(hgb_nbody_create(&g_cached, n, g));
+        g_cached_n = n;
+        g_cached_g = g;
+    }
+    hgb_nbody *h = g_cached;
+    HGB_TRY(hgb_nbody_config(h, g_default_mode, g_default_exchange));
+    HGB_TRY(hgb_nbody_upload(h, planets_aos));
+    HGB_TRY(hgb_nbody_step(h, iterations, nullptr));
+    // reference swaps LOCAL pointers: even states live in planets, odd ones in buffer
+    if (iterations % 2 == 0) return hgb_nbody_download(h, planets_aos, buffer_aos);
+    return hgb_nbody_download(h, buffer_aos, iterations > 1 ? planets_aos : nullptr);
+}
+
+}  // extern "C"
+
+
+// ---- self test of the branch-free IEEE sequences -------------------------------
+// Compares inv_sqrt_ieee(t) with __ddiv_rn(1.0, __dsqrt_rn(t)) bit for bit on
+// `count` operands: random doubles spread over the whole fast-path range, operands
+// clustered the way the nbody kernel produces them (cubes of small sums), and hard
+// cases for both roundings (t next to (m+1/2)^2, roots with all-ones significands).
+__device__ __forceinline__ unsigned long long mix64(unsigned long long z) {
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+__global__ void __launch_bounds__(256)
+inv_sqrt_selftest_kernel(unsigned long long count, unsigned long long seed,
+                         unsigned long long *mismatches, double *first_bad) {
+    unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    unsigned long long bad = 0;
+    for (; i < count; i += stride) {
+        const unsigned long long r = mix64(seed + i), r2 = mix64(r);
+        double t;
+        switch (i & 3) {
+            case 0: {  // any exponent in the fast-path range, random significand
+                unsigned long long e = 0x036 + (r2 % (0x7fe - 0x036));
+                t = __longlong_as_double((long long)((e << 52) | (r >> 12)));
+                break;
+            }
+            case 1: {  // what the kernel sees: t = s^3, s = small sum + EPS
+                double s = (double)(r >> 11) * (1.0 / 9007199254740992.0) * ((r2 & 7) + 1) + kEps;
+                t = __dmul_rn(__dmul_rn(s, s), s);
+                break;
+            }
+            case 2: {  // sqrt hard cases: t adjacent to (m + 1/2)^2
+                double m = __longlong_as_double((long long)((0x3ffull << 52) | (r >> 12)));
+                double h = m + 1.1102230246251565e-16;   // m + ulp/2 (may round; still near-tie)
+                t = __dmul_rn(h, h);
+                long long b = __double_as_longlong(t) + (long long)(r2 % 5) - 2;
+                t = __longlong_as_double(b);
+                if (r2 & 64) t *= 4503599627370496.0;
+                break;
+            }
+            default: {  // roots with all-ones (and nearly all-ones) significands
+                unsigned long long e = 0x200 + (r2 % 0x3ff);
+                unsigned long long sig = 0xFFFFFFFFFFFFFull - (r % 3);
+                double g = __longlong_as_double((long long)((e << 52) | sig));
+                t = __dmul_rn(g, g);
+                long long b = __double_as_longlong(t) + (long long)((r >> 20) % 5) - 2;
+                t = __longlong_as_double(b);
+                break;
+            }
+        }
+        if (range_key(t) >= kRangeLimit) continue;
+        const double want = __ddiv_rn(1.0, __dsqrt_rn(t));
+        const double got = inv_sqrt_ieee(t);
+        if (__double_as_longlong(want) != __double_as_longlong(got)) {
+            if (!bad) first_bad[0] = t;
+            ++bad;
+        }
+    }
+    if (bad) atomicAdd(mismatches, bad);
+}
+
+extern "C" int hgb_selftest_inv_sqrt(unsigned long long count, unsigned long long seed,
+                                     unsigned long long *mismatches, double *first_bad) {
+    HGB_ARG(mismatches, "mismatches == NULL");
+    HGB_TRY(ensure_rank_dev());
+    DevCtx &d = rt().rank_dev;
+    HGB_CUDA(cudaSetDevice(d.device));
+    unsigned long long *dm = nullptr;
+    double *db = nullptr;
+    HGB_CUDA(cudaMalloc(&dm, 8));
+    HGB_CUDA(cudaMalloc(&db, 8));
+    HGB_CUDA(cudaMemsetAsync(dm, 0, 8, d.stream));
+    HGB_CUDA(cudaMemsetAsync(db, 0, 8, d.stream));
+    inv_sqrt_selftest_kernel<<<148 * 8, 256, 0, d.stream>>>(count, seed, dm, db);
+    HGB_LAUNCHED();
+    double fb = 0.0;
+    HGB_CUDA(cudaMemcpyAsync(mismatches, dm, 8, cudaMemcpyDeviceToHost, d.stream));
+    HGB_CUDA(cudaMemcpyAsync(&fb, db, 8, cudaMemcpyDeviceToHost, d.stream));
+    HGB_CUDA(cudaStreamSynchronize(d.stream));
+    if (first_bad) *first_bad = fb;
+    cudaFree(dm);
+    cudaFree(db);
+    return HGB_OK;
+}
+
+namespace hgb {
+void nbody_drop_cache() {
+    hgb_nbody_destroy(g_cached);
+    g_cached = nullptr;
+}
+}  // namespace hgb

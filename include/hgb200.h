@@ -1,0 +1,140 @@
+/*
+ * hgb200.h -- C ABI of libhgb200.so: the B200 (sm_100a) implementation of the
+ * hg-c-benchmarks hot path (all-pairs FP64 nbody step, 2D convolution stencil).
+ *
+ * Plain C, plain pointers and sizes.  Every function returns HGB_OK (0) or a
+ * negative HGB_ERR_* code and never exits, throws or falls back to the CPU;
+ * hgb_last_error() describes the last failure on the calling thread.  The
+ * library owns device memory, streams, pinned staging and NCCL communicators
+ * only; callers allocate and free every host buffer (as the reference's
+ * callers do: src/nbody.c:18-19,45, src/2d-convolution.c:41-43,92).
+ *
+ * Not re-entrant: one host thread drives the library (the reference's run
+ * functions are likewise called from a single thread and fan out inside).
+ *
+ * "reference" below = fendor/hg-c-benchmarks; file:line are relative to it.
+ */
+#ifndef HGB200_H
+#define HGB200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HGB_OK 0
+#define HGB_ERR_ARG (-1)    /* bad argument (null pointer, negative size, kernel larger than padding) */
+#define HGB_ERR_CUDA (-2)   /* a CUDA runtime call or kernel failed */
+#define HGB_ERR_NCCL (-3)   /* NCCL missing or a collective failed */
+#define HGB_ERR_STATE (-4)  /* call order (e.g. step before upload, comm not initialised) */
+#define HGB_ERR_NOGPU (-5)  /* no CUDA device: there is NO CPU fallback */
+
+/* nbody arithmetic modes */
+#define HGB_NBODY_EXACT 0 /* bit-identical to the reference: unfused IEEE ops, j = 0..n-1 in order */
+#define HGB_NBODY_FAST 1  /* FMA-contracted, rsqrt-Newton; ~1e-15 relative per step, not bit-identical */
+/* position exchange between target shards (multi-GPU) */
+#define HGB_EXCHANGE_NCCL 0 /* ncclAllGather after the step kernel */
+#define HGB_EXCHANGE_P2P 1  /* step kernel stores each result into every peer's buffer over NVLink */
+
+/* ---- library ---------------------------------------------------------- */
+const char *hgb_version(void);
+const char *hgb_last_error(void);
+int hgb_device_count(void);                  /* >= 0, or HGB_ERR_NOGPU */
+int hgb_init(void);                          /* optional; everything initialises lazily */
+void hgb_finalize(void);                     /* frees streams, staging, communicators */
+unsigned long long hgb_launch_count(void);   /* kernels launched by this library so far */
+int hgb_flush_l2(void);                      /* overwrite a buffer larger than L2 on every local device */
+/* measured roofline denominators (bench.py; each takes well under a second) */
+int hgb_measure_fp64_peak(double *tflops, double *sm_mhz_est); /* dependent-free DFMA loop */
+int hgb_measure_hbm_copy(double *gbs);                         /* device copy, read+write bytes */
+
+/* ---- one process per GPU (torchrun): communicator over NCCL ------------ */
+/* Rank 0 calls hgb_comm_unique_id, the launcher broadcasts the bytes, every rank
+ * calls hgb_comm_init_rank after cudaSetDevice.  world == 1 needs no NCCL. */
+#define HGB_UNIQUE_ID_BYTES 128
+int hgb_comm_unique_id(void *id_out, int capacity);
+int hgb_comm_init_rank(const void *id, int id_bytes, int rank, int world);
+int hgb_comm_rank(void);
+int hgb_comm_world(void);
+int hgb_comm_barrier(void);
+void hgb_comm_destroy(void);
+
+/* ---- nbody: drop-in --------------------------------------------------- */
+/*
+ * Replaces  void run(Float3D *planets, Float3D *buffer, int number_of_planets,
+ *                    int iterations, int number_of_processes)
+ * (src/nbody/nbody-run.h:46, src/nbody/nbody-run.c:27-37).  planets_aos and
+ * buffer_aos are the caller's Float3D arrays (AoS {x,y,z} doubles,
+ * src/nbody/nbody-util.h:19-23).  Identical semantics, including the
+ * reference's LOCAL pointer swap: on return state k is in planets when k is
+ * even and in buffer when k is odd (k = iterations, iterations-1); with
+ * iterations == 0 or n == 0 nothing is touched.  `ngpus` takes the place of
+ * number_of_processes: GPUs to shard targets over (clamped to the device
+ * count; env HGB_NGPUS overrides).  Uses the mode set by hgb_set_nbody_mode
+ * (default HGB_NBODY_EXACT).
+ */
+int hgb_nbody_run(double *planets_aos, double *buffer_aos, int n, int iterations, int ngpus);
+int hgb_set_nbody_mode(int mode);
+int hgb_set_exchange(int kind);
+
+/* ---- nbody: device-resident (kernel-only timing, many steps) ---------- */
+typedef struct hgb_nbody hgb_nbody;
+/* single process driving `ngpus` local devices (targets sharded evenly) */
+int hgb_nbody_create(hgb_nbody **out, int n, int ngpus);
+/* one process per GPU: this rank owns target shard hgb_comm_rank() of hgb_comm_world() */
+int hgb_nbody_create_rank(hgb_nbody **out, int n);
+int hgb_nbody_config(hgb_nbody *h, int mode, int exchange);
+int hgb_nbody_tune(hgb_nbody *h, int block, int unroll); /* kernel variant; 0 = default */
+int hgb_nbody_upload(hgb_nbody *h, const double *pos_aos);       /* all n bodies */
+/* `iterations` steps; *ms (may be NULL) = device time, CUDA events, max over local devices */
+int hgb_nbody_step(hgb_nbody *h, int iterations, float *ms);
+int hgb_nbody_download(hgb_nbody *h, double *cur_aos, double *prev_aos); /* either may be NULL */
+/* accel() of `count` chosen targets against the current state (subsample parity at n = 2^20) */
+int hgb_nbody_accel_subset(hgb_nbody *h, const int *targets, int count, double *out_aos);
+/* extension, no reference counterpart: U = -G sum_{i<j} (|d|^2+EPS)^(-1/2) */
+int hgb_nbody_energy(hgb_nbody *h, double *energy);
+int hgb_nbody_destroy(hgb_nbody *h);
+/* diagnostic: the kernel's branch-free RN(1/RN(sqrt t)) against the IEEE intrinsics on `count`
+ * random + hard-case operands; *mismatches must come back 0 */
+int hgb_selftest_inv_sqrt(unsigned long long count, unsigned long long seed,
+                          unsigned long long *mismatches, double *first_bad);
+
+/* ---- convolution: drop-in --------------------------------------------- */
+/*
+ * Replaces  void run_on_padded_image(ImageWithPadding **padded_img, Image *kernel,
+ *                                    Args *args, ImageWithPadding **buffer)
+ * (src/convolution/convolution-run.h:70-71, src/convolution/convolution-run.c:41-49),
+ * i.e. `iterations` x { apply_kernel_to_padded_image (:52-62); update_borders
+ * (src/convolution/convolution-util.c:281-294); swap }.
+ * cur / prev: inner_h rows of (inner_w + 2*padding) doubles -- the reference's rows
+ * image[padding .. padding+inner_h-1] INCLUDING their pad columns (read as they
+ * are on the first iteration); the aliased top/bottom pad rows are not passed
+ * (convolution-util.c:394-400 makes them the edge rows).  kernel: kh rows of kw
+ * doubles, correlation, needs kw <= 2*padding+1 and kh <= 2*padding+1.
+ * On return cur = state `iterations`, prev = state iterations-1 (state 0 is the
+ * input `cur`; the input contents of `prev` never matter) -- what the caller of
+ * the reference sees through its swapped pointers.  iterations == 0 touches
+ * nothing.  Bit-identical to the reference for finite data.
+ */
+int hgb_conv_run(double *cur, double *prev, int inner_w, int inner_h, int padding,
+                 const double *kernel, int kw, int kh, int iterations, int ngpus);
+
+/* ---- convolution: device-resident ------------------------------------- */
+typedef struct hgb_conv hgb_conv;
+int hgb_conv_create(hgb_conv **out, int inner_w, int inner_h, int padding, int ngpus);
+int hgb_conv_create_rank(hgb_conv **out, int inner_w, int inner_h, int padding);
+int hgb_conv_set_kernel(hgb_conv *h, const double *kernel, int kw, int kh);
+int hgb_conv_tune(hgb_conv *h, int variant, int band_rows); /* 0 = default; variant 1 = generic kernel */
+int hgb_conv_set_exchange(hgb_conv *h, int kind);           /* HGB_EXCHANGE_NCCL (send/recv) or _P2P (peer copies) */
+/* rank mode: each rank passes ONLY its own band: rows [row0, row0+rows) of the image */
+int hgb_conv_band(hgb_conv *h, int *row0, int *rows);
+int hgb_conv_upload(hgb_conv *h, const double *cur);
+int hgb_conv_step(hgb_conv *h, int iterations, float *ms);
+int hgb_conv_download(hgb_conv *h, double *cur, double *prev /* either may be NULL */);
+/* get_checksum(remove_padding(img)) (convolution-util.c:63-71): sequential row-major sum */
+int hgb_conv_checksum(hgb_conv *h, double *checksum);
+int hgb_conv_destroy(hgb_conv *h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HGB200_H */
