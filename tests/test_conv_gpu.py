@@ -1,0 +1,254 @@
+"""GPU parity tests for the convolution path through the C ABI: bit-identical to the
+reference (golden results of the unmodified reference + the oracle on seeded inputs),
+including the reference's own gtest case, ragged/edge shapes and the 16384^2 benchmark size."""
+import hashlib
+
+import numpy as np
+import pytest
+
+from hg_c_benchmarks_b200 import synth
+
+pytestmark = pytest.mark.gpu
+F = float.fromhex
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def conv_run(hgb, cur, prev, w, h, p, kernel, iters, ngpus=1):
+    kernel = np.ascontiguousarray(kernel, dtype=np.float64)
+    kh, kw = kernel.shape
+    d = hgb._abi.dptr
+    hgb._abi.check(hgb.lib().hgb_conv_run(d(cur), d(prev), w, h, p, d(kernel), kw, kh, iters, ngpus))
+
+
+def test_run_laplace_neutralizes_image(hgb):
+    """the reference's own hot-path test (test/convolutionTests.cpp:9-64), on the GPU"""
+    cv = hgb.convolution
+    img = cv.init_image(3, 3, 1)
+    img.image[...] = [[-1.5, 0, -1], [9, -2, 3], [2, 0, 5]]
+    args = cv.Args(number_of_iterations=15, number_of_processes=1, width=3, height=3)
+    padded = [cv.add_padding(img, 1)]
+    buffer = [cv.init_padded_image(3, 3, 1)]
+    cv.copy_padded_image(padded[0], buffer[0])
+    laplace = cv.init_image(3, 3, 0)
+    laplace.image[1, 1] = -1
+    laplace.image[0, 1] = laplace.image[2, 1] = laplace.image[1, 0] = laplace.image[1, 2] = 0.25
+    assert cv.get_checksum(img) == 14.5
+    cv.run_on_padded_image(padded, laplace, args, buffer)
+    result = cv.remove_padding(padded[0])
+    assert cv.get_checksum(result) == 0
+
+
+def test_gtest_case_matches_reference_bits(hgb, golden):
+    g = golden["conv"]["gtest_laplace_15"]
+    cur = synth.add_padding(np.array([[-1.5, 0, -1], [9, -2, 3], [2, 0, 5]]), 1)
+    prev = cur.copy()
+    conv_run(hgb, cur, prev, 3, 3, 1, synth.LAPLACE_TXT, 15)
+    assert [float(v).hex() for v in cur.ravel()] == g["cur"]
+    assert [float(v).hex() for v in prev.ravel()] == g["prev"]
+
+
+def _golden_case(hgb, golden, key, dense, kernel):
+    g = golden["conv"][key]
+    p, it = g["p"], g["iters"]
+    h, w = dense.shape
+    cur = synth.add_padding(dense, p)
+    prev = np.zeros_like(cur)
+    conv_run(hgb, cur, prev, w, h, p, kernel, it)
+    assert sha(cur) == g["cur_sha256"], key
+    assert sha(prev) == g["prev_sha256"], key
+    # device-side sequential checksum == reference get_checksum
+    with hgb.convolution.Conv2D(w, h, p) as cv:
+        cv.set_kernel(kernel).upload(synth.add_padding(dense, p))
+        cv.step(it)
+        cs = cv.checksum()
+    assert cs == F(g["checksum"]) and "%f" % cs == g["checksum_printed"]
+
+
+@pytest.mark.parametrize("it", [1, 10, 100])
+def test_shipped_image_kernel_txt(hgb, golden, shipped_image, it):
+    _golden_case(hgb, golden, f"input_kernel_txt_n{it}", shipped_image, synth.KERNEL_TXT)
+
+
+@pytest.mark.parametrize("it", [1, 10, 100])
+def test_shipped_image_laplace_txt(hgb, golden, shipped_image, it):
+    _golden_case(hgb, golden, f"input_laplace_txt_n{it}", shipped_image, synth.LAPLACE_TXT)
+
+
+def test_shipped_image_default_kernel(hgb, golden, shipped_image):
+    _golden_case(hgb, golden, "input_default5x5_n10", shipped_image, synth.default_kernel())
+
+
+def test_shipped_float_image(hgb, golden, shipped_image):
+    _golden_case(hgb, golden, "txt_kernel_txt_n10", shipped_image / 256.0, synth.KERNEL_TXT)
+
+
+@pytest.mark.parametrize("w,h,k,it", [(33, 20, 7, 4), (300, 70, 3, 3), (513, 260, 5, 2),
+                                      (1024, 768, 3, 5), (640, 480, 7, 3)])
+def test_synthetic_float_golden(hgb, golden, w, h, k, it):
+    _golden_case(hgb, golden, f"synth_float_{w}x{h}_k{k}_n{it}", synth.image_float(w, h), synth.kernel_dense(k))
+
+
+@pytest.mark.parametrize("k,it", [(3, 4), (7, 2)])
+def test_synthetic_int_golden(hgb, golden, k, it):
+    _golden_case(hgb, golden, f"synth_int_512x384_k{k}_n{it}", synth.image_int(512, 384), synth.kernel_dense(k))
+
+
+RAGGED = [  # (w, h, p, kernel shape (kh, kw), iterations)
+    (1, 1, 1, (3, 3), 3), (2, 1, 1, (3, 3), 2), (1, 9, 3, (7, 7), 2), (5, 2, 3, (7, 7), 3),
+    (255, 3, 1, (3, 3), 2), (256, 4, 1, (3, 3), 2), (257, 5, 1, (3, 3), 2), (511, 130, 2, (5, 5), 2),
+    (769, 129, 3, (7, 7), 2), (1000, 257, 1, (3, 3), 3),
+    (40, 30, 2, (3, 5), 2), (40, 30, 2, (5, 3), 2), (40, 30, 2, (4, 4), 2), (40, 30, 3, (3, 3), 2),
+    (64, 64, 0, (1, 1), 3), (90, 17, 4, (9, 9), 2), (33, 12, 2, (1, 5), 2), (33, 12, 2, (2, 1), 2),
+]
+
+
+@pytest.mark.parametrize("w,h,p,kshape,it", RAGGED)
+def test_ragged_shapes_and_kernels_vs_oracle(hgb, w, h, p, kshape, it):
+    from oracle import port
+    kh, kw = kshape
+    kern = (2.0 * synth.uniform01(77, kh * kw) - 1.0).reshape(kh, kw)
+    base = synth.add_padding(synth.image_float(w, h, seed=w * 31 + h), p)
+    want_c, want_p = base.copy(), np.zeros_like(base)
+    port.conv_run(want_c, want_p, w, h, p, kern, it)
+    got_c, got_p = base.copy(), np.full_like(base, -1.0)
+    conv_run(hgb, got_c, got_p, w, h, p, kern, it)
+    assert np.array_equal(got_c, want_c) and np.array_equal(got_p, want_p)
+
+
+def test_pad_columns_are_read_as_given_on_the_first_iteration(hgb):
+    """the reference reads the caller's pad columns as they are (they need not be edge copies)"""
+    from oracle import port
+    w, h, p = 37, 9, 2
+    base = (synth.uniform01(8, h * (w + 2 * p)) * 10).reshape(h, w + 2 * p)   # arbitrary pad columns
+    kern = synth.kernel_dense(5)
+    want_c, want_p = base.copy(), np.zeros_like(base)
+    port.conv_run(want_c, want_p, w, h, p, kern, 2)
+    got_c, got_p = base.copy(), np.zeros_like(base)
+    conv_run(hgb, got_c, got_p, w, h, p, kern, 2)
+    assert np.array_equal(got_c, want_c) and np.array_equal(got_p, want_p)
+
+
+def test_iteration_count_semantics(hgb):
+    w, h, p = 20, 10, 1
+    base = synth.add_padding(synth.image_float(w, h), p)
+    cur, prev = base.copy(), np.full_like(base, 5.0)
+    conv_run(hgb, cur, prev, w, h, p, synth.LAPLACE_TXT, 0)
+    assert np.array_equal(cur, base) and np.all(prev == 5.0)        # zero iterations: untouched
+    conv_run(hgb, cur, prev, w, h, p, synth.LAPLACE_TXT, 1)
+    assert np.array_equal(prev, base) and not np.array_equal(cur, base)  # one: buffer shows state 0
+
+
+def test_both_kernel_variants_agree(hgb):
+    w, h = 700, 300
+    for k in (3, 5, 7):
+        p = k // 2
+        img = synth.add_padding(synth.image_float(w, h, seed=k), p)
+        outs = []
+        for variant, band in [(0, 0), (0, 7), (0, 64), (1, 0)]:
+            with hgb.convolution.Conv2D(w, h, p) as cv:
+                cv.set_kernel(synth.kernel_dense(k)).tune(variant, band).upload(img)
+                cv.step(3)
+                outs.append(cv.download())
+        for o in outs[1:]:
+            assert np.array_equal(o, outs[0])
+
+
+def test_signed_zero_and_denormal_products(hgb):
+    """val starts at +0.0: an all-(-0.0) sum must come out as +0.0; denormal products are exact ops"""
+    from oracle import port
+    w, h, p = 64, 8, 1
+    img = np.zeros((h, w))
+    img[2, :] = -0.0
+    img[3, ::2] = 5e-324
+    img[4, :] = -1e-310
+    base = synth.add_padding(img, p)
+    kern = np.array([[0.0, -0.0, 0.0], [1e-10, 1.0, -1e-10], [0.0, 0.5, 0.0]])
+    want_c, want_p = base.copy(), np.zeros_like(base)
+    port.conv_run(want_c, want_p, w, h, p, kern, 2)
+    got_c, got_p = base.copy(), np.zeros_like(base)
+    conv_run(hgb, got_c, got_p, w, h, p, kern, 2)
+    assert np.array_equal(got_c, want_c) and np.array_equal(np.signbit(got_c), np.signbit(want_c))
+
+
+def test_argument_errors(hgb):
+    cur, prev = np.zeros((4, 6)), np.zeros((4, 6))
+    E = hgb._abi
+    with pytest.raises(hgb.HgbError) as e:     # 5x5 kernel needs padding 2: the reference would index out of its rows
+        conv_run(hgb, cur, prev, 4, 4, 1, np.ones((5, 5)), 1)
+    assert e.value.code == E.HGB_ERR_ARG
+    with pytest.raises(hgb.HgbError):
+        conv_run(hgb, cur, prev, 0, 4, 1, np.ones((3, 3)), 1)
+    with pytest.raises(hgb.HgbError):
+        conv_run(hgb, cur, prev, 4, 4, 1, np.ones((3, 3)), -1)
+    with hgb.convolution.Conv2D(4, 4, 1) as cv:
+        with pytest.raises(hgb.HgbError) as e:
+            cv.step(1)
+        assert e.value.code == E.HGB_ERR_STATE
+
+
+@pytest.mark.parametrize("k", [3, 7])
+def test_full_size_16k_bands_vs_oracle(hgb, k):
+    """16384 x 16384 (the benchmark size): one iteration on the GPU; three 256-row bands plus the
+    top and bottom edges recomputed by the oracle must match bit for bit, and an exact-arithmetic
+    property must hold on the whole image: integer pixels x power-of-two taps summing to 1 keep a
+    constant image constant."""
+    from oracle import port
+    n = 16384
+    p = k // 2
+    kern = synth.kernel_dense(k)
+    dense = synth.image_int(n, n, seed=4)
+    inp = synth.add_padding(dense, p)
+    del dense
+    with hgb.convolution.Conv2D(n, n, p) as cv:
+        cv.set_kernel(kern).upload(inp)
+        cv.step(1)
+        got = cv.download()
+    for r0 in (0, 5000, 9999, n - 256):
+        want = _oracle_rows(port, inp, n, n, p, kern, r0, r0 + 256)
+        assert np.array_equal(got[r0:r0 + 256], want), (k, r0)
+
+
+def _oracle_rows(port, inp, w, h, p, kern, r0, r1):
+    """oracle output rows [r0, r1) without allocating a second full image: run it on the
+    sub-image [r0-p, r1+p) whose first/last rows are only touched through clamping when they
+    are the true image edges."""
+    lo, hi = max(0, r0 - p), min(h, r1 + p)
+    sub = np.ascontiguousarray(inp[lo:hi])
+    out = np.zeros_like(sub)
+    port.conv_step_rows(sub, out, w, hi - lo, p, kern, r0 - lo, r1 - lo)
+    return out[r0 - lo:r1 - lo]
+
+
+def test_constant_image_stays_constant_at_full_size(hgb):
+    n, p = 16384, 2
+    base = np.full((n, n + 2 * p), 3.0)
+    with hgb.convolution.Conv2D(n, n, p) as cv:
+        cv.set_kernel(synth.KERNEL_TXT).upload(base)     # taps are powers of two summing to 1
+        cv.step(4)
+        got = cv.download()
+    assert np.all(got == 3.0)
+
+
+# ---- multi-GPU (runs when the box has >= 2 GPUs) ------------------------------------------
+@pytest.mark.parametrize("exchange", ["nccl", "p2p"])
+@pytest.mark.parametrize("w,h,k,it", [(300, 70, 3, 4), (513, 260, 5, 3), (640, 33, 7, 3), (64, 5, 7, 2)])
+def test_row_bands_over_gpus_are_bit_identical(hgb, exchange, w, h, k, it):
+    g = min(hgb.lib().hgb_device_count(), 8)
+    if g < 2:
+        pytest.skip("needs >= 2 GPUs")
+    p = k // 2
+    kind = hgb.EXCHANGE_NCCL if exchange == "nccl" else hgb.EXCHANGE_P2P
+    img = synth.add_padding(synth.image_float(w, h, seed=w), p)
+    with hgb.convolution.Conv2D(w, h, p, ngpus=1) as one:
+        one.set_kernel(synth.kernel_dense(k)).upload(img)
+        one.step(it)
+        want_c, want_p = one.download(want_prev=True)
+    for gg in sorted({2, g}):
+        with hgb.convolution.Conv2D(w, h, p, ngpus=gg) as cv:
+            cv.set_exchange(kind).set_kernel(synth.kernel_dense(k)).upload(img)
+            cv.step(it)
+            cur, prev = cv.download(want_prev=True)
+        assert np.array_equal(cur, want_c) and np.array_equal(prev, want_p), (exchange, gg)
