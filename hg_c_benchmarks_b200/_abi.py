@@ -43,13 +43,14 @@ SIGNATURES = {
     "hgb_nbody_create": (C.c_int, [C.POINTER(_vp), C.c_int, C.c_int]),
     "hgb_nbody_create_rank": (C.c_int, [C.POINTER(_vp), C.c_int]),
     "hgb_nbody_config": (C.c_int, [_vp, C.c_int, C.c_int]),
-    "hgb_nbody_tune": (C.c_int, [_vp, C.c_int, C.c_int]),
+    "hgb_nbody_tune": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int]),
     "hgb_nbody_upload": (C.c_int, [_vp, _dp]),
     "hgb_nbody_step": (C.c_int, [_vp, C.c_int, _fp]),
     "hgb_nbody_download": (C.c_int, [_vp, _dp, _dp]),
     "hgb_nbody_accel_subset": (C.c_int, [_vp, _ip, C.c_int, _dp]),
     "hgb_nbody_energy": (C.c_int, [_vp, _dp]),
     "hgb_nbody_destroy": (C.c_int, [_vp]),
+    "hgb_nbody_pairwise": (C.c_int, [_dp, _dp, C.c_int, _dp]),
     "hgb_selftest_inv_sqrt": (C.c_int, [C.c_ulonglong, C.c_ulonglong, C.POINTER(C.c_ulonglong), _dp]),
     "hgb_conv_run": (C.c_int, [_dp, _dp, C.c_int, C.c_int, C.c_int, _dp, C.c_int, C.c_int, C.c_int,
                                C.c_int]),

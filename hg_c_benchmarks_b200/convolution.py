@@ -197,9 +197,10 @@ class Conv2D:
         check(lib().hgb_conv_step(self._h, int(iterations), C.byref(ms)))
         return ms.value
 
-    def download(self, want_prev=False):
+    def download(self, want_prev=False, out=None):
         shape = (self.band()[1], self.w + 2 * self.p)
-        cur = np.empty(shape, dtype=np.float64)
+        cur = np.empty(shape, dtype=np.float64) if out is None else out
+        assert cur.shape == shape
         prev = np.empty(shape, dtype=np.float64) if want_prev else None
         check(lib().hgb_conv_download(self._h, dptr(cur), dptr(prev)))
         return (cur, prev) if want_prev else cur

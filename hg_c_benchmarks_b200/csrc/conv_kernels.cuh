@@ -19,6 +19,8 @@
 #include <cuda_runtime.h>
 #include <cstdint>
 
+#include "async_copy.cuh"
+
 namespace hgb {
 
 constexpr int kLead = 16;      // doubles in front of inner pixel 0 of every device row
@@ -57,40 +59,6 @@ conv_generic_kernel(const double *__restrict__ in, double *__restrict__ out, Ban
         for (int i = 1; i <= g.p; ++i) orow[-i] = val;            // update_borders, left
     if (x == g.W - 1)
         for (int i = 0; i < g.p; ++i) orow[g.W + i] = val;        // update_borders, right
-}
-
-// ---- mbarrier / bulk-copy (TMA engine) primitives -------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void *p) {
-    return (uint32_t)__cvta_generic_to_shared(p);
-}
-__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
-                 "r"(bytes)
-                 : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
-    asm volatile(
-        "{\n"
-        ".reg .pred P1;\n"
-        "WAIT_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
-        "@P1 bra DONE_%=;\n"
-        "bra WAIT_%=;\n"
-        "DONE_%=:\n"
-        "}" ::"r"(smem_u32(bar)),
-        "r"(parity)
-        : "memory");
-}
-// global -> shared bulk copy, completion counted on an mbarrier (SASS: UBLKCP)
-__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
-    asm volatile(
-        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-            smem_u32(dst)),
-        "l"(src), "r"(bytes), "r"(smem_u32(bar))
-        : "memory");
 }
 
 // ---- specialised K x K (K = 2p+1) row-streaming kernel ---------------------

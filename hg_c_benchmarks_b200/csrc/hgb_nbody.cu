@@ -24,7 +24,7 @@ struct hgb_nbody {
     int n = 0, npad = 0, slice = 0, world = 1;
     bool rank_mode = false;
     int mode = HGB_NBODY_EXACT, exchange = HGB_EXCHANGE_NCCL;
-    int block = 0, unroll = 0;
+    int block = 0, unroll = 0, warps = 0;
     int cur = 0;  // state[cur] holds the newest positions
     bool uploaded = false;
     std::vector<NbShard> sh;
@@ -33,36 +33,38 @@ struct hgb_nbody {
 static int g_default_mode = HGB_NBODY_EXACT;
 static int g_default_exchange = HGB_EXCHANGE_NCCL;
 
-template <int BLOCK, int UNROLL>
+template <int BLOCK, int UNROLL, int WARPS>
 static void launch_variant(bool fast, int grid, cudaStream_t st, const double *src, int npad, int n,
                            int t0, int count, const int *tlist, const PeerOut &out, double *out_list) {
     if (fast)
-        nbody_step_kernel<BLOCK, UNROLL, true><<<grid, BLOCK, 0, st>>>(src, npad, n, t0, count, tlist,
-                                                                     out, out_list);
+        nbody_step_kernel<BLOCK, UNROLL, WARPS, true><<<grid, BLOCK, 0, st>>>(src, npad, n, t0, count,
+                                                                            tlist, out, out_list);
     else
-        nbody_step_kernel<BLOCK, UNROLL, false><<<grid, BLOCK, 0, st>>>(src, npad, n, t0, count, tlist,
-                                                                      out, out_list);
+        nbody_step_kernel<BLOCK, UNROLL, WARPS, false><<<grid, BLOCK, 0, st>>>(src, npad, n, t0, count,
+                                                                             tlist, out, out_list);
 }
 
 static int launch_step(const hgb_nbody *h, const NbShard &s, const double *src, int t0, int count,
                        const int *tlist, const PeerOut &out, double *out_list) {
     if (count <= 0) return HGB_OK;
     const bool fast = h->mode == HGB_NBODY_FAST;
-    int block = h->block ? h->block : 128;
-    int unroll = h->unroll ? h->unroll : 2;
+    const int block = h->block ? h->block : 128;
+    const int unroll = h->unroll ? h->unroll : 2;
+    const int warps = h->warps ? h->warps : 24;   // measured on B200: 24 >= 32 > 40 (profiles/r1_nbody_sweep.txt)
     const int grid = (count + block - 1) / block;
     cudaStream_t st = s.dev->stream;
-#define HGB_V(B, U)                                                                             \
-    if (block == B && unroll == U) {                                                            \
-        launch_variant<B, U>(fast, grid, st, src, h->npad, h->n, t0, count, tlist, out, out_list); \
-        HGB_LAUNCHED();                                                                         \
-        return HGB_OK;                                                                          \
+#define HGB_V(B, U, W)                                                                             \
+    if (block == B && unroll == U && warps == W) {                                                 \
+        launch_variant<B, U, W>(fast, grid, st, src, h->npad, h->n, t0, count, tlist, out, out_list); \
+        HGB_LAUNCHED();                                                                            \
+        return HGB_OK;                                                                             \
     }
-    HGB_V(64, 1) HGB_V(64, 2) HGB_V(64, 4)
-    HGB_V(128, 1) HGB_V(128, 2) HGB_V(128, 4)
-    HGB_V(256, 1) HGB_V(256, 2) HGB_V(256, 4)
+#define HGB_VW(B, U) HGB_V(B, U, 24) HGB_V(B, U, 32) HGB_V(B, U, 40)
+    HGB_VW(128, 1) HGB_VW(128, 2) HGB_VW(128, 4)
+    HGB_VW(256, 1) HGB_VW(256, 2) HGB_VW(256, 4)
+#undef HGB_VW
 #undef HGB_V
-    set_error("no nbody kernel variant block=%d unroll=%d", block, unroll);
+    set_error("no nbody kernel variant block=%d unroll=%d warps=%d", block, unroll, warps);
     return HGB_ERR_ARG;
 }
 
@@ -174,12 +176,14 @@ int hgb_nbody_config(hgb_nbody *h, int mode, int exchange) {
     return HGB_OK;
 }
 
-int hgb_nbody_tune(hgb_nbody *h, int block, int unroll) {
+int hgb_nbody_tune(hgb_nbody *h, int block, int unroll, int warps) {
     HGB_ARG(h, "handle");
-    HGB_ARG(block == 0 || block == 64 || block == 128 || block == 256, "block in {64,128,256}");
+    HGB_ARG(block == 0 || block == 128 || block == 256, "block in {128,256}");
     HGB_ARG(unroll == 0 || unroll == 1 || unroll == 2 || unroll == 4, "unroll in {1,2,4}");
+    HGB_ARG(warps == 0 || warps == 24 || warps == 32 || warps == 40, "warps in {24,32,40}");
     h->block = block;
     h->unroll = unroll;
+    h->warps = warps;
     return HGB_OK;
 }
 
@@ -423,6 +427,37 @@ inv_sqrt_selftest_kernel(unsigned long long count, unsigned long long seed,
         }
     }
     if (bad) atomicAdd(mismatches, bad);
+}
+
+// pair_wise_accel (reference src/nbody/nbody-run.c:6-15) for `count` sources in order:
+// acc += d * factor, no G scaling.  One thread; this is the symbol-level drop-in, not a fast path.
+__global__ void nbody_pairwise_kernel(const double *__restrict__ p1, const double *__restrict__ p2,
+                                      int count, double *__restrict__ acc) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    double ax = acc[0], ay = acc[1], az = acc[2];
+    unsigned key = 0;
+    for (int j = 0; j < count; ++j)
+        interact<false, true>(p1[0], p1[1], p1[2], p2[3 * j], p2[3 * j + 1], p2[3 * j + 2], ax, ay, az, key);
+    acc[0] = ax; acc[1] = ay; acc[2] = az;
+}
+
+extern "C" int hgb_nbody_pairwise(const double *p1, const double *p2_aos, int count, double *acc_inout) {
+    HGB_ARG(p1 && p2_aos && acc_inout && count >= 0, "pairwise arguments");
+    HGB_TRY(ensure_rank_dev());
+    DevCtx &d = rt().rank_dev;
+    HGB_CUDA(cudaSetDevice(d.device));
+    double *buf = nullptr;
+    const size_t doubles = 6 + 3ull * count;
+    HGB_CUDA(cudaMalloc(&buf, doubles * sizeof(double)));
+    HGB_CUDA(cudaMemcpyAsync(buf, p1, 24, cudaMemcpyHostToDevice, d.stream));
+    HGB_CUDA(cudaMemcpyAsync(buf + 3, acc_inout, 24, cudaMemcpyHostToDevice, d.stream));
+    if (count) HGB_CUDA(cudaMemcpyAsync(buf + 6, p2_aos, 24ull * count, cudaMemcpyHostToDevice, d.stream));
+    nbody_pairwise_kernel<<<1, 32, 0, d.stream>>>(buf, buf + 6, count, buf + 3);
+    HGB_LAUNCHED();
+    HGB_CUDA(cudaMemcpyAsync(acc_inout, buf + 3, 24, cudaMemcpyDeviceToHost, d.stream));
+    HGB_CUDA(cudaStreamSynchronize(d.stream));
+    cudaFree(buf);
+    return HGB_OK;
 }
 
 extern "C" int hgb_selftest_inv_sqrt(unsigned long long count, unsigned long long seed,

@@ -59,8 +59,8 @@ class NBody:
             check(lib().hgb_nbody_create(C.byref(self._h), self.n, int(ngpus)))
         check(lib().hgb_nbody_config(self._h, int(mode), int(exchange)))
 
-    def tune(self, block=0, unroll=0):
-        check(lib().hgb_nbody_tune(self._h, int(block), int(unroll)))
+    def tune(self, block=0, unroll=0, warps=0):
+        check(lib().hgb_nbody_tune(self._h, int(block), int(unroll), int(warps)))
         return self
 
     def upload(self, pos):

@@ -83,7 +83,9 @@ int hgb_nbody_create(hgb_nbody **out, int n, int ngpus);
 /* one process per GPU: this rank owns target shard hgb_comm_rank() of hgb_comm_world() */
 int hgb_nbody_create_rank(hgb_nbody **out, int n);
 int hgb_nbody_config(hgb_nbody *h, int mode, int exchange);
-int hgb_nbody_tune(hgb_nbody *h, int block, int unroll); /* kernel variant; 0 = default */
+/* kernel variant; 0 = default: threads per CTA {128,256}, sources per unrolled group/2 {1,2,4},
+ * resident warps per SM the register allocation allows {24,32,40} */
+int hgb_nbody_tune(hgb_nbody *h, int block, int unroll, int warps);
 int hgb_nbody_upload(hgb_nbody *h, const double *pos_aos);       /* all n bodies */
 /* `iterations` steps; *ms (may be NULL) = device time, CUDA events, max over local devices */
 int hgb_nbody_step(hgb_nbody *h, int iterations, float *ms);
@@ -93,6 +95,9 @@ int hgb_nbody_accel_subset(hgb_nbody *h, const int *targets, int count, double *
 /* extension, no reference counterpart: U = -G sum_{i<j} (|d|^2+EPS)^(-1/2) */
 int hgb_nbody_energy(hgb_nbody *h, double *energy);
 int hgb_nbody_destroy(hgb_nbody *h);
+/* pair_wise_accel(p1, p2[j], &acc) for j = 0..count-1 in order (src/nbody/nbody-run.c:6-15):
+ * acc_inout[3] += d * factor, no G scaling.  Symbol-level drop-in, one GPU thread. */
+int hgb_nbody_pairwise(const double *p1, const double *p2_aos, int count, double *acc_inout);
 /* diagnostic: the kernel's branch-free RN(1/RN(sqrt t)) against the IEEE intrinsics on `count`
  * random + hard-case operands; *mismatches must come back 0 */
 int hgb_selftest_inv_sqrt(unsigned long long count, unsigned long long seed,

@@ -81,12 +81,13 @@ def test_every_kernel_variant_gives_the_same_bits(hgb):
     pos = synth.plummer(n, seed=7)
     want = np.zeros_like(pos)
     port.nbody_step_range(pos, want, 0, n)
-    for block in (64, 128, 256):
+    for block in (128, 256):
         for unroll in (1, 2, 4):
-            with hgb.nbody.NBody(n) as nb:
-                nb.tune(block, unroll).upload(pos)
-                nb.step(1)
-                assert np.array_equal(nb.download(), want), (block, unroll)
+            for warps in (24, 32, 40):
+                with hgb.nbody.NBody(n) as nb:
+                    nb.tune(block, unroll, warps).upload(pos)
+                    nb.step(1)
+                    assert np.array_equal(nb.download(), want), (block, unroll, warps)
 
 
 def test_overflow_and_nonfinite_operands_take_the_ieee_slow_path(hgb):

@@ -1,0 +1,26 @@
+"""Short profiling target for ncu --set full: one nbody step (EXACT and FAST) and a few
+convolution iterations.  Usage: python tools/prof_target.py [nbody|conv]"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import hg_c_benchmarks_b200 as H  # noqa: E402
+from hg_c_benchmarks_b200 import synth  # noqa: E402
+
+what = sys.argv[1] if len(sys.argv) > 1 else "nbody"
+if what == "nbody":
+    n = 131072
+    pos = synth.uniform_cube(n, seed=1)
+    for mode in (H.NBODY_EXACT, H.NBODY_FAST):
+        with H.nbody.NBody(n, mode=mode) as nb:
+            nb.upload(pos)
+            print("mode", mode, "ms", nb.step(1), nb.step(1))
+else:
+    n = 16384
+    dense = synth.image_float(n, n, seed=3)
+    for k in (3, 7):
+        p = k // 2
+        with H.convolution.Conv2D(n, n, p) as cv:
+            cv.set_kernel(synth.kernel_dense(k)).upload(synth.add_padding(dense, p))
+            print("k", k, "ms", cv.step(2), cv.step(2))
+H.lib().hgb_finalize()
