@@ -23,6 +23,7 @@ sys.path.insert(0, ROOT)
 
 import numpy as np  # noqa: E402
 
+OUT = sys.stdout
 N_BODIES = 1 << 20
 CONV_N = 16384
 CONV_ITERS = 10
@@ -135,7 +136,7 @@ def run_reference(args):
             "cpu_baseline": {"value": value, "unit": "interactions/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": "interactions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=OUT, flush=True)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -177,6 +178,12 @@ def cpu_baseline():
 
 
 def main():
+    # stdout carries exactly ONE JSON line: libraries that print to fd 1 (NCCL's version banner)
+    # are sent to stderr, the JSON goes to a private duplicate of the original stdout
+    global OUT
+    sys.stdout.flush()
+    OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
@@ -340,7 +347,7 @@ def main():
         }
         if world == 1 and not args.skip_cpu:
             line["cpu_baseline"] = cpu_baseline()
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=OUT, flush=True)
     barrier()
     L.hgb_finalize()
     if dist:

@@ -31,7 +31,8 @@ struct Taps { double k[kMaxTaps]; };   // kernel parameter => constant bank oper
 struct BandGeom {
     int W, H;        // inner image size (global)
     int p;           // reference padding
-    int row0, rows;  // this band: global rows [row0, row0+rows)
+    int row0, rows;  // this band: global rows [row0, row0+rows) -- defines the addressing
+    int crow0, crows;  // rows this LAUNCH computes (a sub-range of the band: boundary / interior split)
     int halo;        // halo rows stored above/below the band
     int dp;          // device row pitch in doubles
 };
@@ -45,7 +46,7 @@ __global__ void __launch_bounds__(256)
 conv_generic_kernel(const double *__restrict__ in, double *__restrict__ out, BandGeom g,
                     const double *__restrict__ taps, int kw, int kh) {
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
-    const int y = g.row0 + blockIdx.y;
+    const int y = g.crow0 + blockIdx.y;
     if (x >= g.W) return;
     double val = 0.0;
     for (int ky = 0; ky < kh; ++ky) {
@@ -92,8 +93,8 @@ conv_stream_kernel(const double *__restrict__ in, double *__restrict__ out, Band
     uint64_t *full = reinterpret_cast<uint64_t *>(ring + (size_t)NST * K * ROWW);
 
     const int x0 = blockIdx.x * TW;
-    const int y0 = g.row0 + blockIdx.y * chunk;                  // first output row (global)
-    const int nrows = min(chunk, g.row0 + g.rows - y0);          // output rows of this CTA
+    const int y0 = g.crow0 + blockIdx.y * chunk;                 // first output row (global)
+    const int nrows = min(chunk, g.crow0 + g.crows - y0);        // output rows of this CTA
     const int nin = nrows + 2 * P;                               // input rows streamed
     const int nstages = (nin + K - 1) / K;
     const int tid = threadIdx.x;

@@ -84,6 +84,8 @@ struct DevCtx {
     int device = -1;
     cudaStream_t stream = nullptr;  // all kernels + collectives of this device
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr, ev_step = nullptr;
+    cudaStream_t stream2 = nullptr; // boundary rows + halo exchange, overlapped with the interior
+    cudaEvent_t ev_bnd[2] = {nullptr, nullptr}, ev_int[2] = {nullptr, nullptr}, ev_join = nullptr;
     ncclComm_t comm = nullptr;      // single-process communicator (ncclCommInitAll)
     void *flush_buf = nullptr;      // L2 flush scratch
 };

@@ -28,6 +28,7 @@ struct hgb_conv {
     std::vector<double> taps_host;
     bool have_kernel = false;
     int variant = 0, chunk = 0, exchange = HGB_EXCHANGE_NCCL;
+    bool overlap = true;   // boundary/interior split with the exchange under the interior kernel
     int cur = 0;
     bool uploaded = false;
     std::vector<CvShard> sh;
@@ -37,6 +38,7 @@ static BandGeom geom(const hgb_conv *h, const CvShard &s) {
     BandGeom g;
     g.W = h->W; g.H = h->H; g.p = h->p;
     g.row0 = s.row0; g.rows = s.rows;
+    g.crow0 = s.row0; g.crows = s.rows;
     g.halo = h->halo; g.dp = h->dp;
     return g;
 }
@@ -74,8 +76,10 @@ static int cv_setup(hgb_conv *h) {
     return HGB_OK;
 }
 
+// rows [crow0, crow0+crows) of the band on stream `st`
 template <int K, int NST>
-static int launch_stream(const hgb_conv *h, const CvShard &s, const double *in, double *out) {
+static int launch_stream(const hgb_conv *h, const CvShard &s, const double *in, double *out, int crow0,
+                         int crows, cudaStream_t st) {
     using Cfg = ConvCfg<K, kTW, 2, NST>;
     auto kern = conv_stream_kernel<K, kTW, 2, NST>;
     static bool attr_done[16] = {false};
@@ -84,66 +88,75 @@ static int launch_stream(const hgb_conv *h, const CvShard &s, const double *in, 
         attr_done[s.dev->device & 15] = true;
     }
     int chunk = h->chunk > 0 ? h->chunk : 128;
-    if (chunk > s.rows) chunk = s.rows;
-    dim3 grid((h->W + kTW - 1) / kTW, (s.rows + chunk - 1) / chunk);
-    kern<<<grid, Cfg::THREADS, Cfg::SMEM, s.dev->stream>>>(in, out, geom(h, s), chunk, h->taps);
+    if (chunk > crows) chunk = crows;
+    BandGeom g = geom(h, s);
+    g.crow0 = crow0;
+    g.crows = crows;
+    dim3 grid((h->W + kTW - 1) / kTW, (crows + chunk - 1) / chunk);
+    kern<<<grid, Cfg::THREADS, Cfg::SMEM, st>>>(in, out, g, chunk, h->taps);
     HGB_LAUNCHED();
     return HGB_OK;
 }
 
-static int launch_conv(const hgb_conv *h, const CvShard &s, const double *in, double *out) {
-    if (s.rows <= 0) return HGB_OK;
+static int launch_conv(const hgb_conv *h, const CvShard &s, const double *in, double *out, int crow0,
+                       int crows, cudaStream_t st) {
+    if (crows <= 0) return HGB_OK;
     const bool square = h->kw == h->kh && h->kw == 2 * h->p + 1;
     if (h->variant != 1 && square) {
-        if (h->kw == 3) return launch_stream<3, 4>(h, s, in, out);
-        if (h->kw == 5) return launch_stream<5, 3>(h, s, in, out);
-        if (h->kw == 7) return launch_stream<7, 3>(h, s, in, out);
+        if (h->kw == 3) return launch_stream<3, 4>(h, s, in, out, crow0, crows, st);
+        if (h->kw == 5) return launch_stream<5, 3>(h, s, in, out, crow0, crows, st);
+        if (h->kw == 7) return launch_stream<7, 3>(h, s, in, out, crow0, crows, st);
     }
-    dim3 grid((h->W + 255) / 256, s.rows);
-    conv_generic_kernel<<<grid, 256, 0, s.dev->stream>>>(in, out, geom(h, s), s.taps_dev, h->kw, h->kh);
+    BandGeom g = geom(h, s);
+    g.crow0 = crow0;
+    g.crows = crows;
+    dim3 grid((h->W + 255) / 256, crows);
+    conv_generic_kernel<<<grid, 256, 0, st>>>(in, out, g, s.taps_dev, h->kw, h->kh);
     HGB_LAUNCHED();
     return HGB_OK;
 }
 
 // exchange the p edge rows of state `b` between neighbouring bands
-static int halo_exchange(hgb_conv *h, int b) {
+static int halo_exchange(hgb_conv *h, int b, bool side = false) {
+    // side: run on the boundary stream (stream2) so the interior kernel overlaps the exchange
+    auto xs = [side](const CvShard &s) { return side ? s.dev->stream2 : s.dev->stream; };
     if (h->active <= 1 || h->p == 0) return HGB_OK;
     const size_t cnt = (size_t)h->p * h->dp;     // p full device rows (pad columns included)
     if (!h->rank_mode && h->exchange == HGB_EXCHANGE_P2P) {
         // peer copies on the RECEIVER's stream after the sender's kernel finished
         for (CvShard &s : h->sh) {
             HGB_CUDA(cudaSetDevice(s.dev->device));
-            HGB_CUDA(cudaEventRecord(s.dev->ev_step, s.dev->stream));
+            HGB_CUDA(cudaEventRecord(s.dev->ev_step, xs(s)));
         }
         for (CvShard &s : h->sh) {
             if (s.rows <= 0) continue;
             HGB_CUDA(cudaSetDevice(s.dev->device));
             if (s.index > 0) {
                 CvShard &up = h->sh[s.index - 1];
-                HGB_CUDA(cudaStreamWaitEvent(s.dev->stream, up.dev->ev_step, 0));
+                HGB_CUDA(cudaStreamWaitEvent(xs(s), up.dev->ev_step, 0));
                 HGB_CUDA(cudaMemcpyPeerAsync(s.img[b], s.dev->device,
                                              up.img[b] + (size_t)up.rows * h->dp, up.dev->device,
-                                             cnt * sizeof(double), s.dev->stream));
+                                             cnt * sizeof(double), xs(s)));
             }
             if (s.index < h->active - 1) {
                 CvShard &dn = h->sh[s.index + 1];
-                HGB_CUDA(cudaStreamWaitEvent(s.dev->stream, dn.dev->ev_step, 0));
+                HGB_CUDA(cudaStreamWaitEvent(xs(s), dn.dev->ev_step, 0));
                 HGB_CUDA(cudaMemcpyPeerAsync(s.img[b] + (size_t)(h->halo + s.rows) * h->dp,
                                              s.dev->device, dn.img[b] + (size_t)h->halo * h->dp,
-                                             dn.dev->device, cnt * sizeof(double), s.dev->stream));
+                                             dn.dev->device, cnt * sizeof(double), xs(s)));
             }
         }
         // a band may only be overwritten (next iteration writes the OTHER buffer, but the
         // one after that writes this one) once its neighbours have pulled their halos
         for (CvShard &s : h->sh) {
             HGB_CUDA(cudaSetDevice(s.dev->device));
-            HGB_CUDA(cudaEventRecord(s.dev->ev_step, s.dev->stream));
+            HGB_CUDA(cudaEventRecord(s.dev->ev_step, xs(s)));
         }
         for (CvShard &s : h->sh)
             for (int d = -1; d <= 1; d += 2) {
                 int o = s.index + d;
                 if (o < 0 || o >= h->active) continue;
-                HGB_CUDA(cudaStreamWaitEvent(s.dev->stream, h->sh[o].dev->ev_step, 0));
+                HGB_CUDA(cudaStreamWaitEvent(xs(s), h->sh[o].dev->ev_step, 0));
             }
         return HGB_OK;
     }
@@ -154,14 +167,14 @@ static int halo_exchange(hgb_conv *h, int b) {
         double *base = s.img[b];
         if (s.index > 0) {
             HGB_NCCL(nccl().Send(base + (size_t)h->halo * h->dp, cnt, ncclDouble, s.index - 1, comm,
-                                 s.dev->stream));
-            HGB_NCCL(nccl().Recv(base, cnt, ncclDouble, s.index - 1, comm, s.dev->stream));
+                                 xs(s)));
+            HGB_NCCL(nccl().Recv(base, cnt, ncclDouble, s.index - 1, comm, xs(s)));
         }
         if (s.index < h->active - 1) {
             HGB_NCCL(nccl().Send(base + (size_t)s.rows * h->dp, cnt, ncclDouble, s.index + 1, comm,
-                                 s.dev->stream));
+                                 xs(s)));
             HGB_NCCL(nccl().Recv(base + (size_t)(h->halo + s.rows) * h->dp, cnt, ncclDouble,
-                                 s.index + 1, comm, s.dev->stream));
+                                 s.index + 1, comm, xs(s)));
         }
     }
     HGB_NCCL(nccl().GroupEnd());
@@ -246,8 +259,9 @@ int hgb_conv_set_kernel(hgb_conv *h, const double *kernel, int kw, int kh) {
 }
 
 int hgb_conv_tune(hgb_conv *h, int variant, int band_rows) {
-    HGB_ARG(h && variant >= 0 && variant <= 1 && band_rows >= 0, "handle / variant / band_rows");
-    h->variant = variant;
+    HGB_ARG(h && variant >= 0 && variant <= 3 && band_rows >= 0, "handle / variant / band_rows");
+    h->variant = variant & 1;
+    h->overlap = !(variant & 2);
     h->chunk = band_rows;
     return HGB_OK;
 }
@@ -309,15 +323,55 @@ int hgb_conv_step(hgb_conv *h, int iterations, float *ms) {
         HGB_CUDA(cudaSetDevice(s.dev->device));
         HGB_CUDA(cudaEventRecord(s.dev->ev_begin, s.dev->stream));
     }
+    // Multi-GPU: split every band into boundary rows (first/last kBnd rows, stream2, followed by
+    // the halo exchange) and interior rows (main stream), so the exchange of iteration t
+    // runs under the interior kernel of iteration t.  Events alternate by iteration parity.
+    constexpr int kBnd = 32;
+    bool overlap = h->overlap && h->active > 1 && h->p > 0;
+    for (CvShard &s : h->sh)
+        if (s.rows > 0 && s.rows < 4 * kBnd) overlap = false;
+    if (overlap)
+        for (CvShard &s : h->sh) {   // stream2 starts after whatever the main stream did before
+            HGB_CUDA(cudaSetDevice(s.dev->device));
+            HGB_CUDA(cudaStreamWaitEvent(s.dev->stream2, s.dev->ev_begin, 0));
+        }
     for (int it = 0; it < iterations; ++it) {
         const int cur = h->cur, nxt = cur ^ 1;
-        for (CvShard &s : h->sh) {
-            HGB_CUDA(cudaSetDevice(s.dev->device));
-            HGB_TRY(launch_conv(h, s, s.img[cur], s.img[nxt]));
+        if (!overlap) {
+            for (CvShard &s : h->sh) {
+                HGB_CUDA(cudaSetDevice(s.dev->device));
+                HGB_TRY(launch_conv(h, s, s.img[cur], s.img[nxt], s.row0, s.rows, s.dev->stream));
+            }
+            HGB_TRY(halo_exchange(h, nxt));
+        } else {
+            const int e = it & 1, pe = e ^ 1;
+            for (CvShard &s : h->sh) {
+                if (s.rows <= 0) continue;
+                HGB_CUDA(cudaSetDevice(s.dev->device));
+                cudaStream_t sb = s.dev->stream2;
+                if (it > 0) HGB_CUDA(cudaStreamWaitEvent(sb, s.dev->ev_int[pe], 0));
+                HGB_TRY(launch_conv(h, s, s.img[cur], s.img[nxt], s.row0, kBnd, sb));
+                HGB_TRY(launch_conv(h, s, s.img[cur], s.img[nxt], s.row0 + s.rows - kBnd, kBnd, sb));
+                HGB_CUDA(cudaEventRecord(s.dev->ev_bnd[e], sb));
+            }
+            HGB_TRY(halo_exchange(h, nxt, true));
+            for (CvShard &s : h->sh) {
+                if (s.rows <= 0) continue;
+                HGB_CUDA(cudaSetDevice(s.dev->device));
+                if (it > 0) HGB_CUDA(cudaStreamWaitEvent(s.dev->stream, s.dev->ev_bnd[pe], 0));
+                HGB_TRY(launch_conv(h, s, s.img[cur], s.img[nxt], s.row0 + kBnd, s.rows - 2 * kBnd,
+                                    s.dev->stream));
+                HGB_CUDA(cudaEventRecord(s.dev->ev_int[e], s.dev->stream));
+            }
         }
-        HGB_TRY(halo_exchange(h, nxt));
         h->cur = nxt;
     }
+    if (overlap)
+        for (CvShard &s : h->sh) {   // join: the main stream (and its timing event) covers stream2
+            HGB_CUDA(cudaSetDevice(s.dev->device));
+            HGB_CUDA(cudaEventRecord(s.dev->ev_join, s.dev->stream2));
+            HGB_CUDA(cudaStreamWaitEvent(s.dev->stream, s.dev->ev_join, 0));
+        }
     float worst = 0.f;
     for (CvShard &s : h->sh) {
         HGB_CUDA(cudaSetDevice(s.dev->device));

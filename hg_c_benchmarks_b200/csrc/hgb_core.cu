@@ -88,6 +88,12 @@ int init_dev(DevCtx &d, int device) {
     HGB_CUDA(cudaEventCreate(&d.ev_begin));
     HGB_CUDA(cudaEventCreate(&d.ev_end));
     HGB_CUDA(cudaEventCreateWithFlags(&d.ev_step, cudaEventDisableTiming));
+    HGB_CUDA(cudaStreamCreateWithFlags(&d.stream2, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+        HGB_CUDA(cudaEventCreateWithFlags(&d.ev_bnd[i], cudaEventDisableTiming));
+        HGB_CUDA(cudaEventCreateWithFlags(&d.ev_int[i], cudaEventDisableTiming));
+    }
+    HGB_CUDA(cudaEventCreateWithFlags(&d.ev_join, cudaEventDisableTiming));
     return HGB_OK;
 }
 
@@ -227,6 +233,10 @@ void hgb_finalize(void) {
         cudaEventDestroy(d.ev_begin);
         cudaEventDestroy(d.ev_end);
         cudaEventDestroy(d.ev_step);
+        cudaStreamSynchronize(d.stream2);
+        for (int i = 0; i < 2; ++i) { cudaEventDestroy(d.ev_bnd[i]); cudaEventDestroy(d.ev_int[i]); }
+        cudaEventDestroy(d.ev_join);
+        cudaStreamDestroy(d.stream2);
         cudaStreamDestroy(d.stream);
         d = DevCtx();
     };

@@ -128,7 +128,9 @@ typedef struct hgb_conv hgb_conv;
 int hgb_conv_create(hgb_conv **out, int inner_w, int inner_h, int padding, int ngpus);
 int hgb_conv_create_rank(hgb_conv **out, int inner_w, int inner_h, int padding);
 int hgb_conv_set_kernel(hgb_conv *h, const double *kernel, int kw, int kh);
-int hgb_conv_tune(hgb_conv *h, int variant, int band_rows); /* 0 = default; variant 1 = generic kernel */
+/* variant bit 0: generic kernel instead of the specialised one; bit 1: no boundary/interior overlap
+ * in the multi-GPU step; band_rows: output rows per CTA (0 = default 128) */
+int hgb_conv_tune(hgb_conv *h, int variant, int band_rows);
 int hgb_conv_set_exchange(hgb_conv *h, int kind);           /* HGB_EXCHANGE_NCCL (send/recv) or _P2P (peer copies) */
 /* rank mode: each rank passes ONLY its own band: rows [row0, row0+rows) of the image */
 int hgb_conv_band(hgb_conv *h, int *row0, int *rows);

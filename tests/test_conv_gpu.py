@@ -234,7 +234,8 @@ def test_constant_image_stays_constant_at_full_size(hgb):
 
 # ---- multi-GPU (runs when the box has >= 2 GPUs) ------------------------------------------
 @pytest.mark.parametrize("exchange", ["nccl", "p2p"])
-@pytest.mark.parametrize("w,h,k,it", [(300, 70, 3, 4), (513, 260, 5, 3), (640, 33, 7, 3), (64, 5, 7, 2)])
+@pytest.mark.parametrize("w,h,k,it", [(300, 70, 3, 4), (513, 260, 5, 3), (640, 33, 7, 3), (64, 5, 7, 2),
+                                      (300, 1100, 3, 5), (513, 1300, 7, 4), (260, 2049, 5, 3)])  # tall: overlapped path
 def test_row_bands_over_gpus_are_bit_identical(hgb, exchange, w, h, k, it):
     g = min(hgb.lib().hgb_device_count(), 8)
     if g < 2:
