@@ -18,6 +18,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cstdint>
+#include <type_traits>
 
 #include "async_copy.cuh"
 
@@ -143,39 +144,51 @@ conv_stream_kernel(const double *__restrict__ in, double *__restrict__ out, Band
                 double v[NIN];
 #pragma unroll
                 for (int q = 0; q < NIN; ++q) v[q] = srow[q];
+                // steady-state rows feed all K output rows; the first/last K-1 rows of a chunk only
+                // some of them (no output above/below the chunk): one warp-uniform test per row
+                auto row_body = [&](auto full_tag) {
+                    constexpr bool FULL = decltype(full_tag)::value;
+                    constexpr bool EDGE = K <= 5;
 #pragma unroll
-                for (int ky = 0; ky < K; ++ky) {
-                    const int a = (ph - ky + K) % K;   // compile-time accumulator slot of row i-ky
+                    for (int ky = 0; ky < K; ++ky) {
+                        const int a = (ph - ky + K) % K;   // compile-time accumulator slot of row i-ky
+                        if (!FULL && (i - ky < 0 || i - ky >= nrows)) continue;
 #pragma unroll
-                    for (int c = 0; c < C; ++c) {
-                        double val = (ky == 0) ? 0.0 : acc[a][c];
+                        for (int c = 0; c < C; ++c) {
+                            double val = (ky == 0) ? 0.0 : acc[a][c];
 #pragma unroll
-                        for (int kx = 0; kx < K; ++kx)
-                            val = __dadd_rn(val, __dmul_rn(taps.k[ky * K + kx], v[c + kx]));
-                        acc[a][c] = val;
-                    }
-                    if (ky == K - 1 && i >= K - 1 && any_col) {      // output row i-(K-1) is complete
-                        const int gy = y0 + i - (K - 1);
-                        double *orow = out + band_row_off(g, gy) + kLead;
-                        if (C == 2 && xt + 1 < g.W) {
-                            *reinterpret_cast<double2 *>(orow + xt) = make_double2(acc[a][0], acc[a][1]);
-                        } else {
+                            for (int kx = 0; kx < K; ++kx)
+                                val = __dadd_rn(val, __dmul_rn(taps.k[ky * K + kx], v[c + kx]));
+                            acc[a][c] = val;
+                        }
+                        if (ky == K - 1 && any_col && (EDGE || i >= K - 1)) {   // output row i-(K-1) is complete
+                            const int gy = y0 + i - (K - 1);
+                            double *orow = out + band_row_off(g, gy) + kLead;
+                            if (C == 2 && xt + 1 < g.W) {
+                                *reinterpret_cast<double2 *>(orow + xt) = make_double2(acc[a][0], acc[a][1]);
+                            } else {
+#pragma unroll
+                                for (int c = 0; c < C; ++c)
+                                    if (xt + c < g.W) orow[xt + c] = acc[a][c];
+                            }
+                            if (xt == 0) {                                // update_borders, left
+#pragma unroll
+                                for (int q = 1; q <= P; ++q) orow[-q] = acc[a][0];
+                            }
 #pragma unroll
                             for (int c = 0; c < C; ++c)
-                                if (xt + c < g.W) orow[xt + c] = acc[a][c];
+                                if (xt + c == g.W - 1) {                  // update_borders, right
+#pragma unroll
+                                    for (int q = 0; q < P; ++q) orow[g.W + q] = acc[a][c];
+                                }
                         }
-                        if (xt == 0) {                                // update_borders, left
-#pragma unroll
-                            for (int q = 1; q <= P; ++q) orow[-q] = acc[a][0];
-                        }
-#pragma unroll
-                        for (int c = 0; c < C; ++c)
-                            if (xt + c == g.W - 1) {                  // update_borders, right
-#pragma unroll
-                                for (int q = 0; q < P; ++q) orow[g.W + q] = acc[a][c];
-                            }
                     }
-                }
+                };
+                // (7x7: the duplicated body would not fit the instruction cache -- measured slower --
+                //  so it computes the few useless edge taps instead)
+                constexpr bool EDGE = K <= 5;
+                if (!EDGE || (i >= K - 1 && i < nrows)) row_body(std::true_type{});
+                else row_body(std::false_type{});
             }
         }
         __syncthreads();   // everyone is done reading this slot

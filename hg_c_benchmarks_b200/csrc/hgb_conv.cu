@@ -87,7 +87,10 @@ static int launch_stream(const hgb_conv *h, const CvShard &s, const double *in, 
         HGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
         attr_done[s.dev->device & 15] = true;
     }
-    int chunk = h->chunk > 0 ? h->chunk : 128;
+    // output rows per CTA: small chunks keep the concurrently streamed rows close together in
+    // DRAM (3x3 is HBM-bound); larger ones amortise the K-1 extra input rows (5x5, 7x7 are
+    // FP64-bound).  Measured on B200: profiles/r1_conv_chunk_sweep.txt
+    int chunk = h->chunk > 0 ? h->chunk : (K == 3 ? 8 : K == 5 ? 32 : 128);
     if (chunk > crows) chunk = crows;
     BandGeom g = geom(h, s);
     g.crow0 = crow0;

@@ -88,7 +88,11 @@ int init_dev(DevCtx &d, int device) {
     HGB_CUDA(cudaEventCreate(&d.ev_begin));
     HGB_CUDA(cudaEventCreate(&d.ev_end));
     HGB_CUDA(cudaEventCreateWithFlags(&d.ev_step, cudaEventDisableTiming));
-    HGB_CUDA(cudaStreamCreateWithFlags(&d.stream2, cudaStreamNonBlocking));
+    {   // boundary rows + halo exchange must win SM slots against the bulk interior kernel
+        int lo = 0, hi = 0;
+        HGB_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        HGB_CUDA(cudaStreamCreateWithPriority(&d.stream2, cudaStreamNonBlocking, hi));
+    }
     for (int i = 0; i < 2; ++i) {
         HGB_CUDA(cudaEventCreateWithFlags(&d.ev_bnd[i], cudaEventDisableTiming));
         HGB_CUDA(cudaEventCreateWithFlags(&d.ev_int[i], cudaEventDisableTiming));
