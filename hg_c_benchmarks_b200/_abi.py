@@ -58,6 +58,7 @@ SIGNATURES = {
     "hgb_conv_create_rank": (C.c_int, [C.POINTER(_vp), C.c_int, C.c_int, C.c_int]),
     "hgb_conv_set_kernel": (C.c_int, [_vp, _dp, C.c_int, C.c_int]),
     "hgb_conv_tune": (C.c_int, [_vp, C.c_int, C.c_int]),
+    "hgb_conv_set_depth": (C.c_int, [_vp, C.c_int]),
     "hgb_conv_set_exchange": (C.c_int, [_vp, C.c_int]),
     "hgb_conv_band": (C.c_int, [_vp, _ip, _ip]),
     "hgb_conv_upload": (C.c_int, [_vp, _dp]),

@@ -182,6 +182,13 @@ class Conv2D:
         check(lib().hgb_conv_tune(self._h, int(variant), int(band_rows)))
         return self
 
+    def set_depth(self, depth=0):
+        """iterations per halo exchange (multi-GPU); returns the depth in effect"""
+        rc = lib().hgb_conv_set_depth(self._h, int(depth))
+        if rc < 0:
+            check(rc)
+        return rc
+
     def set_exchange(self, kind):
         check(lib().hgb_conv_set_exchange(self._h, int(kind)))
         return self

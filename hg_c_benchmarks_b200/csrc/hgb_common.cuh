@@ -105,6 +105,7 @@ Runtime &rt();
 
 int device_count_checked(int *count);       // HGB_ERR_NOGPU when there is none
 int resolve_ngpus(int requested, int *out); // clamp + HGB_NGPUS override
+bool oversubscribed(int g);                 // g shards on fewer devices (HGB_VIRTUAL_GPUS)
 int ensure_devices(int g);                  // streams/events for devices 0..g-1
 int ensure_sp_comm(int g);                  // ncclCommInitAll over devices 0..g-1
 int ensure_peer_access(int g);

@@ -22,7 +22,9 @@ struct CvShard {
 struct hgb_conv {
     int W = 0, H = 0, p = 0, world = 1, active = 1;  // active = ranks that own rows
     bool rank_mode = false;
-    int dp = 0, halo = 0;
+    int dp = 0, halo = 0;     // halo = rows stored above/below a band (addressing); >= depth * p
+    int depth_req = 0;        // iterations per halo exchange asked for (0 = automatic)
+    int valid_xr = 0;         // halo rows of the current state that hold the neighbours' data
     int kw = 0, kh = 0;
     Taps taps;
     std::vector<double> taps_host;
@@ -51,9 +53,23 @@ static void band_of(int H, int active, int i, int *row0, int *rows) {
     *rows = base + (i < rem ? 1 : 0);
 }
 
+constexpr int kBnd = 32;   // boundary rows per side computed ahead of the exchange (and halo capacity)
+
+// Communication-avoiding halo: exchange depth*p rows once every `depth` iterations and let a band
+// recompute the shrinking fringe in between (iteration t of a cycle covers (depth-1-t)*p rows beyond
+// the band).  Same arithmetic per pixel => bit-identical; exchange latency is amortised depth-fold.
+static int eff_depth(const hgb_conv *h) {
+    if (h->active <= 1 || h->p <= 0) return 1;
+    int minrows = h->H / h->active;
+    int d = h->depth_req > 0 ? h->depth_req : 8;
+    if (d > h->halo / h->p) d = h->halo / h->p;
+    if (d > minrows / h->p) d = minrows / h->p;
+    return d < 1 ? 1 : d;
+}
+
 static int cv_setup(hgb_conv *h) {
     const int p = h->p;
-    h->halo = p;
+    h->halo = (h->world > 1 && p > 0 && p < kBnd) ? kBnd : p;
     // every band must be at least p rows tall so halos come from direct neighbours only
     int act = h->world;
     const int need = p > 0 ? p : 1;
@@ -124,7 +140,8 @@ static int halo_exchange(hgb_conv *h, int b, bool side = false) {
     // side: run on the boundary stream (stream2) so the interior kernel overlaps the exchange
     auto xs = [side](const CvShard &s) { return side ? s.dev->stream2 : s.dev->stream; };
     if (h->active <= 1 || h->p == 0) return HGB_OK;
-    const size_t cnt = (size_t)h->p * h->dp;     // p full device rows (pad columns included)
+    const int xr = eff_depth(h) * h->p;          // rows exchanged per side
+    const size_t cnt = (size_t)xr * h->dp;       // full device rows (pad columns included)
     if (!h->rank_mode && h->exchange == HGB_EXCHANGE_P2P) {
         // peer copies on the RECEIVER's stream after the sender's kernel finished
         for (CvShard &s : h->sh) {
@@ -137,9 +154,9 @@ static int halo_exchange(hgb_conv *h, int b, bool side = false) {
             if (s.index > 0) {
                 CvShard &up = h->sh[s.index - 1];
                 HGB_CUDA(cudaStreamWaitEvent(xs(s), up.dev->ev_step, 0));
-                HGB_CUDA(cudaMemcpyPeerAsync(s.img[b], s.dev->device,
-                                             up.img[b] + (size_t)up.rows * h->dp, up.dev->device,
-                                             cnt * sizeof(double), xs(s)));
+                HGB_CUDA(cudaMemcpyPeerAsync(s.img[b] + (size_t)(h->halo - xr) * h->dp, s.dev->device,
+                                             up.img[b] + (size_t)(h->halo + up.rows - xr) * h->dp,
+                                             up.dev->device, cnt * sizeof(double), xs(s)));
             }
             if (s.index < h->active - 1) {
                 CvShard &dn = h->sh[s.index + 1];
@@ -161,6 +178,7 @@ static int halo_exchange(hgb_conv *h, int b, bool side = false) {
                 if (o < 0 || o >= h->active) continue;
                 HGB_CUDA(cudaStreamWaitEvent(xs(s), h->sh[o].dev->ev_step, 0));
             }
+        h->valid_xr = xr;
         return HGB_OK;
     }
     HGB_NCCL(nccl().GroupStart());
@@ -171,16 +189,18 @@ static int halo_exchange(hgb_conv *h, int b, bool side = false) {
         if (s.index > 0) {
             HGB_NCCL(nccl().Send(base + (size_t)h->halo * h->dp, cnt, ncclDouble, s.index - 1, comm,
                                  xs(s)));
-            HGB_NCCL(nccl().Recv(base, cnt, ncclDouble, s.index - 1, comm, xs(s)));
+            HGB_NCCL(nccl().Recv(base + (size_t)(h->halo - xr) * h->dp, cnt, ncclDouble, s.index - 1, comm,
+                                 xs(s)));
         }
         if (s.index < h->active - 1) {
-            HGB_NCCL(nccl().Send(base + (size_t)s.rows * h->dp, cnt, ncclDouble, s.index + 1, comm,
-                                 xs(s)));
+            HGB_NCCL(nccl().Send(base + (size_t)(h->halo + s.rows - xr) * h->dp, cnt, ncclDouble,
+                                 s.index + 1, comm, xs(s)));
             HGB_NCCL(nccl().Recv(base + (size_t)(h->halo + s.rows) * h->dp, cnt, ncclDouble,
                                  s.index + 1, comm, xs(s)));
         }
     }
     HGB_NCCL(nccl().GroupEnd());
+    h->valid_xr = xr;
     return HGB_OK;
 }
 
@@ -217,6 +237,7 @@ int hgb_conv_create(hgb_conv **out, int inner_w, int inner_h, int padding, int n
     h->sh.resize(g);
     for (int i = 0; i < g; ++i) { h->sh[i].dev = &rt().devs[i]; h->sh[i].index = i; }
     int rc = cv_setup(h);
+    if (rc == HGB_OK && g > 1 && oversubscribed(g)) rc = hgb_conv_set_exchange(h, HGB_EXCHANGE_P2P);
     if (rc != HGB_OK) { hgb_conv_destroy(h); return rc; }
     *out = h;
     return HGB_OK;
@@ -269,8 +290,15 @@ int hgb_conv_tune(hgb_conv *h, int variant, int band_rows) {
     return HGB_OK;
 }
 
+int hgb_conv_set_depth(hgb_conv *h, int depth) {
+    HGB_ARG(h && depth >= 0, "handle / depth");
+    h->depth_req = depth;
+    return eff_depth(h);
+}
+
 int hgb_conv_set_exchange(hgb_conv *h, int kind) {
     HGB_ARG(h && (kind == HGB_EXCHANGE_NCCL || kind == HGB_EXCHANGE_P2P), "handle / kind");
+    if (!h->rank_mode && h->world > 1 && oversubscribed(h->world)) kind = HGB_EXCHANGE_P2P;
     if (kind == HGB_EXCHANGE_P2P && h->world > 1) {
         if (h->rank_mode) { set_error("peer exchange needs the single-process handle"); return HGB_ERR_STATE; }
         HGB_TRY(ensure_peer_access(h->world));
@@ -309,6 +337,7 @@ int hgb_conv_upload(hgb_conv *h, const double *cur) {
     }
     h->cur = 0;
     h->uploaded = true;
+    h->valid_xr = h->rank_mode ? 0 : h->halo;
     if (h->rank_mode && h->world > 1) HGB_TRY(halo_exchange(h, 0));
     for (CvShard &s : h->sh) HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
     return HGB_OK;
@@ -326,48 +355,64 @@ int hgb_conv_step(hgb_conv *h, int iterations, float *ms) {
         HGB_CUDA(cudaSetDevice(s.dev->device));
         HGB_CUDA(cudaEventRecord(s.dev->ev_begin, s.dev->stream));
     }
-    // Multi-GPU: split every band into boundary rows (first/last kBnd rows, stream2, followed by
-    // the halo exchange) and interior rows (main stream), so the exchange of iteration t
-    // runs under the interior kernel of iteration t.  Events alternate by iteration parity.
-    constexpr int kBnd = 32;
+    // Multi-GPU schedule, per cycle of d <= depth iterations (see eff_depth):
+    //   iterations 0..d-2: one launch over the band plus its shrinking fringe (main stream);
+    //   iteration d-1:     the band's first/last kBnd rows on stream2 followed by the halo exchange,
+    //                      the interior rows on the main stream -- the exchange runs under the interior.
+    // ev_pre (main -> stream2): everything before the last iteration is done;
+    // ev_x   (stream2 -> main): boundary rows and halos of the finished cycle are in place.
     bool overlap = h->overlap && h->active > 1 && h->p > 0;
     for (CvShard &s : h->sh)
         if (s.rows > 0 && s.rows < 4 * kBnd) overlap = false;
+    const int depth = eff_depth(h);
+    if (h->active > 1 && h->valid_xr < depth * h->p && iterations > 0)
+        HGB_TRY(halo_exchange(h, h->cur));   // the depth was raised after the last exchange
     if (overlap)
         for (CvShard &s : h->sh) {   // stream2 starts after whatever the main stream did before
             HGB_CUDA(cudaSetDevice(s.dev->device));
             HGB_CUDA(cudaStreamWaitEvent(s.dev->stream2, s.dev->ev_begin, 0));
         }
-    for (int it = 0; it < iterations; ++it) {
-        const int cur = h->cur, nxt = cur ^ 1;
-        if (!overlap) {
-            for (CvShard &s : h->sh) {
-                HGB_CUDA(cudaSetDevice(s.dev->device));
-                HGB_TRY(launch_conv(h, s, s.img[cur], s.img[nxt], s.row0, s.rows, s.dev->stream));
-            }
-            HGB_TRY(halo_exchange(h, nxt));
-        } else {
-            const int e = it & 1, pe = e ^ 1;
+    for (int it = 0, cycle = 0; it < iterations; ++cycle) {
+        const int d = min(depth, iterations - it);
+        if (overlap && cycle > 0)
             for (CvShard &s : h->sh) {
                 if (s.rows <= 0) continue;
                 HGB_CUDA(cudaSetDevice(s.dev->device));
-                cudaStream_t sb = s.dev->stream2;
-                if (it > 0) HGB_CUDA(cudaStreamWaitEvent(sb, s.dev->ev_int[pe], 0));
-                HGB_TRY(launch_conv(h, s, s.img[cur], s.img[nxt], s.row0, kBnd, sb));
-                HGB_TRY(launch_conv(h, s, s.img[cur], s.img[nxt], s.row0 + s.rows - kBnd, kBnd, sb));
-                HGB_CUDA(cudaEventRecord(s.dev->ev_bnd[e], sb));
+                HGB_CUDA(cudaStreamWaitEvent(s.dev->stream, s.dev->ev_bnd[0], 0));   // ev_x
             }
-            HGB_TRY(halo_exchange(h, nxt, true));
-            for (CvShard &s : h->sh) {
-                if (s.rows <= 0) continue;
-                HGB_CUDA(cudaSetDevice(s.dev->device));
-                if (it > 0) HGB_CUDA(cudaStreamWaitEvent(s.dev->stream, s.dev->ev_bnd[pe], 0));
-                HGB_TRY(launch_conv(h, s, s.img[cur], s.img[nxt], s.row0 + kBnd, s.rows - 2 * kBnd,
-                                    s.dev->stream));
-                HGB_CUDA(cudaEventRecord(s.dev->ev_int[e], s.dev->stream));
+        for (int t = 0; t < d; ++t, ++it) {
+            const int cur = h->cur, nxt = cur ^ 1;
+            const bool last = t == d - 1;
+            const int ext = (d - 1 - t) * h->p;        // fringe rows beyond the band (0 on the last)
+            if (!last || !overlap) {
+                for (CvShard &s : h->sh) {
+                    if (s.rows <= 0) continue;
+                    HGB_CUDA(cudaSetDevice(s.dev->device));
+                    const int lo = max(0, s.row0 - ext), hi = min(h->H, s.row0 + s.rows + ext);
+                    HGB_TRY(launch_conv(h, s, s.img[cur], s.img[nxt], lo, hi - lo, s.dev->stream));
+                }
+                if (last) HGB_TRY(halo_exchange(h, nxt));
+            } else {
+                for (CvShard &s : h->sh) {
+                    if (s.rows <= 0) continue;
+                    HGB_CUDA(cudaSetDevice(s.dev->device));
+                    cudaStream_t sb = s.dev->stream2;
+                    HGB_CUDA(cudaEventRecord(s.dev->ev_int[0], s.dev->stream));      // ev_pre
+                    HGB_CUDA(cudaStreamWaitEvent(sb, s.dev->ev_int[0], 0));
+                    HGB_TRY(launch_conv(h, s, s.img[cur], s.img[nxt], s.row0, kBnd, sb));
+                    HGB_TRY(launch_conv(h, s, s.img[cur], s.img[nxt], s.row0 + s.rows - kBnd, kBnd, sb));
+                }
+                HGB_TRY(halo_exchange(h, nxt, true));
+                for (CvShard &s : h->sh) {
+                    if (s.rows <= 0) continue;
+                    HGB_CUDA(cudaSetDevice(s.dev->device));
+                    HGB_CUDA(cudaEventRecord(s.dev->ev_bnd[0], s.dev->stream2));     // ev_x
+                    HGB_TRY(launch_conv(h, s, s.img[cur], s.img[nxt], s.row0 + kBnd, s.rows - 2 * kBnd,
+                                        s.dev->stream));
+                }
             }
+            h->cur = nxt;
         }
-        h->cur = nxt;
     }
     if (overlap)
         for (CvShard &s : h->sh) {   // join: the main stream (and its timing event) covers stream2

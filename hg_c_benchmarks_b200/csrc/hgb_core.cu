@@ -67,6 +67,20 @@ int device_count_checked(int *count) {
     return HGB_OK;
 }
 
+// HGB_VIRTUAL_GPUS=v (test aid): shard over up to v "GPUs" even when fewer devices exist; shard i
+// then lives on device i % count with its own streams, and exchanges use peer copies / peer
+// stores (NCCL refuses two ranks on one device).  Lets one GPU exercise all the sharding logic.
+static int virtual_gpus() {
+    const char *env = getenv("HGB_VIRTUAL_GPUS");
+    int v = env ? atoi(env) : 0;
+    return v > 8 ? 8 : v;
+}
+
+bool oversubscribed(int g) {
+    int c = 0;
+    return device_count_checked(&c) == HGB_OK && g > c;
+}
+
 int resolve_ngpus(int requested, int *out) {
     int c = 0;
     HGB_TRY(device_count_checked(&c));
@@ -75,7 +89,8 @@ int resolve_ngpus(int requested, int *out) {
         int v = atoi(env);
         if (v > 0) g = v;
     }
-    if (g > c) g = c;
+    const int cap = virtual_gpus() > c ? virtual_gpus() : c;
+    if (g > cap) g = cap;
     *out = g;
     return HGB_OK;
 }
@@ -104,9 +119,9 @@ int init_dev(DevCtx &d, int device) {
 int ensure_devices(int g) {
     int c = 0;
     HGB_TRY(device_count_checked(&c));
-    HGB_ARG(g >= 1 && g <= c, "gpu count out of range");
+    HGB_ARG(g >= 1 && (g <= c || g <= virtual_gpus()), "gpu count out of range");
     if ((int)g_rt.devs.size() < g) g_rt.devs.resize(g);
-    for (int i = 0; i < g; ++i) HGB_TRY(init_dev(g_rt.devs[i], i));
+    for (int i = 0; i < g; ++i) HGB_TRY(init_dev(g_rt.devs[i], i % c));
     HGB_CUDA(cudaSetDevice(0));
     return HGB_OK;
 }
@@ -115,6 +130,10 @@ int ensure_sp_comm(int g) {
     if (g <= 1) return HGB_OK;
     HGB_TRY(ensure_devices(g));
     if (g_rt.comm_devs == g) return HGB_OK;
+    if (oversubscribed(g)) {
+        set_error("NCCL cannot put %d ranks on fewer devices (HGB_VIRTUAL_GPUS uses peer exchange)", g);
+        return HGB_ERR_STATE;
+    }
     HGB_TRY(nccl_load());
     if (g_rt.comm_devs) {
         for (int i = 0; i < g_rt.comm_devs; ++i) {
@@ -134,6 +153,9 @@ int ensure_sp_comm(int g) {
 
 int ensure_peer_access(int g) {
     HGB_TRY(ensure_devices(g));
+    int c = 0;
+    HGB_TRY(device_count_checked(&c));
+    if (g > c) g = c;   // virtual shards share devices
     for (int a = 0; a < g; ++a) {
         HGB_CUDA(cudaSetDevice(a));
         for (int b = 0; b < g; ++b) {

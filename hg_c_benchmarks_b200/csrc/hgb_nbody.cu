@@ -130,6 +130,10 @@ int hgb_nbody_create(hgb_nbody **out, int n, int ngpus) {
         h->sh[i].index = i;
     }
     int rc = nb_alloc(h);
+    if (rc == HGB_OK && g > 1 && (h->exchange == HGB_EXCHANGE_P2P || oversubscribed(g))) {
+        h->exchange = HGB_EXCHANGE_P2P;   // virtual shards share a device: NCCL cannot be used
+        rc = ensure_peer_access(g);
+    }
     if (rc != HGB_OK) { hgb_nbody_destroy(h); return rc; }
     *out = h;
     return HGB_OK;
@@ -164,6 +168,7 @@ int hgb_nbody_config(hgb_nbody *h, int mode, int exchange) {
     HGB_ARG(h, "handle");
     HGB_ARG(mode == HGB_NBODY_EXACT || mode == HGB_NBODY_FAST, "mode");
     HGB_ARG(exchange == HGB_EXCHANGE_NCCL || exchange == HGB_EXCHANGE_P2P, "exchange");
+    if (!h->rank_mode && h->world > 1 && oversubscribed(h->world)) exchange = HGB_EXCHANGE_P2P;
     if (exchange == HGB_EXCHANGE_P2P && h->world > 1) {
         if (h->rank_mode) {
             set_error("peer-store exchange needs the single-process multi-GPU handle");

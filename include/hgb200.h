@@ -131,6 +131,10 @@ int hgb_conv_set_kernel(hgb_conv *h, const double *kernel, int kw, int kh);
 /* variant bit 0: generic kernel instead of the specialised one; bit 1: no boundary/interior overlap
  * in the multi-GPU step; band_rows: output rows per CTA (0 = default 128) */
 int hgb_conv_tune(hgb_conv *h, int variant, int band_rows);
+/* iterations per halo exchange (communication-avoiding deep halo, multi-GPU only): depth*p rows
+ * travel once per `depth` iterations, the fringe is recomputed in between; 0 = automatic (8, capped
+ * by 32/p and the band height).  Returns the depth in effect (>= 1) or a negative error. */
+int hgb_conv_set_depth(hgb_conv *h, int depth);
 int hgb_conv_set_exchange(hgb_conv *h, int kind);           /* HGB_EXCHANGE_NCCL (send/recv) or _P2P (peer copies) */
 /* rank mode: each rank passes ONLY its own band: rows [row0, row0+rows) of the image */
 int hgb_conv_band(hgb_conv *h, int *row0, int *rows);

@@ -232,14 +232,23 @@ def test_constant_image_stays_constant_at_full_size(hgb):
     assert np.all(got == 3.0)
 
 
-# ---- multi-GPU (runs when the box has >= 2 GPUs) ------------------------------------------
-@pytest.mark.parametrize("exchange", ["nccl", "p2p"])
-@pytest.mark.parametrize("w,h,k,it", [(300, 70, 3, 4), (513, 260, 5, 3), (640, 33, 7, 3), (64, 5, 7, 2),
-                                      (300, 1100, 3, 5), (513, 1300, 7, 4), (260, 2049, 5, 3)])  # tall: overlapped path
-def test_row_bands_over_gpus_are_bit_identical(hgb, exchange, w, h, k, it):
+# ---- multi-GPU: real devices when the box has them, else HGB_VIRTUAL_GPUS shards on one device ----
+def _gpu_counts(hgb, monkeypatch, exchange):
     g = min(hgb.lib().hgb_device_count(), 8)
     if g < 2:
-        pytest.skip("needs >= 2 GPUs")
+        if exchange == "nccl":
+            pytest.skip("NCCL needs >= 2 devices (virtual shards use peer copies)")
+        monkeypatch.setenv("HGB_VIRTUAL_GPUS", "4")
+        return [2, 3, 4]
+    return sorted({2, g})
+
+
+@pytest.mark.parametrize("exchange", ["nccl", "p2p"])
+@pytest.mark.parametrize("depth", [0, 1, 3])
+@pytest.mark.parametrize("w,h,k,it", [(300, 70, 3, 4), (513, 260, 5, 3), (640, 33, 7, 3), (64, 5, 7, 2),
+                                      (300, 1100, 3, 21), (513, 1300, 7, 9), (260, 2049, 5, 10)])  # tall: overlapped path
+def test_row_bands_over_gpus_are_bit_identical(hgb, monkeypatch, exchange, depth, w, h, k, it):
+    counts = _gpu_counts(hgb, monkeypatch, exchange)
     p = k // 2
     kind = hgb.EXCHANGE_NCCL if exchange == "nccl" else hgb.EXCHANGE_P2P
     img = synth.add_padding(synth.image_float(w, h, seed=w), p)
@@ -247,9 +256,30 @@ def test_row_bands_over_gpus_are_bit_identical(hgb, exchange, w, h, k, it):
         one.set_kernel(synth.kernel_dense(k)).upload(img)
         one.step(it)
         want_c, want_p = one.download(want_prev=True)
-    for gg in sorted({2, g}):
+    for gg in counts:
         with hgb.convolution.Conv2D(w, h, p, ngpus=gg) as cv:
             cv.set_exchange(kind).set_kernel(synth.kernel_dense(k)).upload(img)
+            d = cv.set_depth(depth)
+            assert d >= 1 and (depth == 0 or d <= depth)
             cv.step(it)
             cur, prev = cv.download(want_prev=True)
-        assert np.array_equal(cur, want_c) and np.array_equal(prev, want_p), (exchange, gg)
+        assert np.array_equal(cur, want_c) and np.array_equal(prev, want_p), (exchange, gg, d)
+
+
+def test_depth_can_change_between_steps_and_split_steps_agree(hgb, monkeypatch):
+    counts = _gpu_counts(hgb, monkeypatch, "p2p")
+    w, h, k, p = 384, 1500, 3, 1
+    img = synth.add_padding(synth.image_float(w, h, seed=9), p)
+    with hgb.convolution.Conv2D(w, h, p, ngpus=1) as one:
+        one.set_kernel(synth.kernel_dense(k)).upload(img)
+        one.step(17)
+        want = one.download()
+    with hgb.convolution.Conv2D(w, h, p, ngpus=counts[-1]) as cv:
+        cv.set_exchange(hgb.EXCHANGE_P2P).set_kernel(synth.kernel_dense(k)).upload(img)
+        cv.set_depth(2)
+        cv.step(5)
+        cv.set_depth(16)          # deeper than the halos exchanged so far: step re-exchanges first
+        cv.step(11)
+        cv.set_depth(1)
+        cv.step(1)
+        assert np.array_equal(cv.download(), want)

@@ -205,10 +205,13 @@ def test_errors_are_reported_not_hidden(hgb):
 # ---- multi-GPU (runs when the box has >= 2 GPUs) ------------------------------------------
 @pytest.mark.parametrize("exchange", ["nccl", "p2p"])
 @pytest.mark.parametrize("n,iters", [(5000, 3), (2048, 2), (70001, 2)])
-def test_target_sharding_over_gpus_is_bit_identical(hgb, exchange, n, iters):
+def test_target_sharding_over_gpus_is_bit_identical(hgb, monkeypatch, exchange, n, iters):
     g = min(ngpus(hgb), 8)
-    if g < 2:
-        pytest.skip("needs >= 2 GPUs")
+    if g < 2:       # one device: HGB_VIRTUAL_GPUS shards on it, results stored peer-to-peer
+        if exchange == "nccl":
+            pytest.skip("NCCL needs >= 2 devices (virtual shards use peer stores)")
+        monkeypatch.setenv("HGB_VIRTUAL_GPUS", "4")
+        g = 4
     kind = hgb.EXCHANGE_NCCL if exchange == "nccl" else hgb.EXCHANGE_P2P
     pos = synth.plummer(n, seed=n)
     with hgb.nbody.NBody(n, ngpus=1) as one:
