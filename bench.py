@@ -30,7 +30,7 @@ CONV_ITERS = 10          # the config's iteration count (used by the end-to-end 
 CONV_TIMED = 100         # device-resident timing runs 10 x 10 iterations back to back: at 8 GPUs ten
                          # iterations last ~1 ms, comparable to the host skew between ranks after a barrier
 FLOP_PER_INTERACTION = 19          # 3 sub, 3 mul+3 add (+EPS), 2 mul, sqrt, div, 3 mul+3 add
-FP64_INSTR_PER_INTERACTION = 30    # exact mode: 17 plain + 8 (IEEE sqrt) + 5 (IEEE reciprocal) FP64-pipe ops
+FP64_INSTR_PER_INTERACTION = 29    # exact mode: 17 plain + 8 (IEEE sqrt) + 4 (IEEE reciprocal) FP64-pipe ops (tools/sass_loop.py)
 BYTES_PER_PIXEL = 16               # 8 B read + 8 B written per inner pixel per iteration
 
 
@@ -343,7 +343,7 @@ def main():
                          "traffic": None, "per_gpu": True,
                          "peak_source": "in-run dependent-free DFMA probe (MEASURED_PEAKS.json has no FP64 figure)",
                          "fp64_pipe_util": value / world * FP64_INSTR_PER_INTERACTION / (tf.value / 2 * 1e12),
-                         "fp64_pipe_util_note": "30 FP64-pipe instructions per interaction in exact mode vs measured DFMA issue rate",
+                         "fp64_pipe_util_note": f"{FP64_INSTR_PER_INTERACTION} FP64-pipe instructions per interaction in exact mode (SASS count) vs measured DFMA issue rate",
                          "probe_sm_mhz": mhz.value, "hbm_copy_probe_gbs": gbs.value},
             "conv": conv,
         }

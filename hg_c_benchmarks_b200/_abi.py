@@ -49,6 +49,10 @@ SIGNATURES = {
     "hgb_nbody_download": (C.c_int, [_vp, _dp, _dp]),
     "hgb_nbody_accel_subset": (C.c_int, [_vp, _ip, C.c_int, _dp]),
     "hgb_nbody_energy": (C.c_int, [_vp, _dp]),
+    "hgb_nbody_set_dynamics": (C.c_int, [_vp, _dp, _dp, C.c_double]),
+    "hgb_nbody_integrate": (C.c_int, [_vp, C.c_int, _fp]),
+    "hgb_nbody_download_velocities": (C.c_int, [_vp, _dp]),
+    "hgb_nbody_total_energy": (C.c_int, [_vp, _dp, _dp]),
     "hgb_nbody_destroy": (C.c_int, [_vp]),
     "hgb_nbody_pairwise": (C.c_int, [_dp, _dp, C.c_int, _dp]),
     "hgb_selftest_inv_sqrt": (C.c_int, [C.c_ulonglong, C.c_ulonglong, C.POINTER(C.c_ulonglong), _dp]),

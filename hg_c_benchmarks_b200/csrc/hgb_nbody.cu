@@ -15,6 +15,8 @@ struct NbShard {
     double *state[2] = {nullptr, nullptr};  // ping-pong SoA, 3*npad doubles each
     double *stage = nullptr;     // AoS staging, 3*npad doubles
     double *partials = nullptr;  // energy block sums
+    double *vel = nullptr;       // integrator extension: SoA velocities, 3*npad (own slice is live)
+    double *mass = nullptr;      // integrator extension: npad masses, zero beyond n
     int *tlist = nullptr;
     int tlist_cap = 0;
 };
@@ -27,6 +29,8 @@ struct hgb_nbody {
     int block = 0, unroll = 0, warps = 0;
     int cur = 0;  // state[cur] holds the newest positions
     bool uploaded = false;
+    bool dynamics = false;  // hgb_nbody_set_dynamics was called
+    double dt = 0.0;
     std::vector<NbShard> sh;
 };
 
@@ -77,7 +81,7 @@ static int nb_alloc(hgb_nbody *h) {
             HGB_CUDA(cudaMemsetAsync(s.state[b], 0, bytes, s.dev->stream));
         }
         HGB_CUDA(cudaMalloc(&s.stage, bytes));
-        HGB_CUDA(cudaMalloc(&s.partials, sizeof(double) * (h->slice / 64 + 2)));
+        HGB_CUDA(cudaMalloc(&s.partials, sizeof(double) * 2 * (h->slice / 64 + 2)));
     }
     return HGB_OK;
 }
@@ -105,6 +109,8 @@ int hgb_nbody_destroy(hgb_nbody *h) {
         cudaFree(s.state[1]);
         cudaFree(s.stage);
         cudaFree(s.partials);
+        if (s.vel) cudaFree(s.vel);
+        if (s.mass) cudaFree(s.mass);
         if (s.tlist) cudaFree(s.tlist);
     }
     delete h;
@@ -208,9 +214,9 @@ int hgb_nbody_upload(hgb_nbody *h, const double *pos_aos) {
     return HGB_OK;
 }
 
-int hgb_nbody_step(hgb_nbody *h, int iterations, float *ms) {
-    HGB_ARG(h && iterations >= 0, "handle / iterations");
-    if (!h->uploaded) { set_error("hgb_nbody_step before hgb_nbody_upload"); return HGB_ERR_STATE; }
+// `iterations` x { step kernel on every shard; exchange the new positions }.  dyn: the integrator
+// extension (mass-weighted sources, velocity/position update in the epilogue) instead of accel().
+static int nb_advance(hgb_nbody *h, int iterations, float *ms, bool dyn) {
     const bool multi = h->world > 1;
     const bool p2p = multi && h->exchange == HGB_EXCHANGE_P2P;
     if (multi && !p2p && !h->rank_mode) HGB_TRY(ensure_sp_comm(h->world));
@@ -231,7 +237,16 @@ int hgb_nbody_step(hgb_nbody *h, int iterations, float *ms) {
             }
             const int t0 = s.index * h->slice;
             const int count = max(0, min(h->n, t0 + h->slice) - t0);
-            HGB_TRY(launch_step(h, s, s.state[cur], t0, count, nullptr, out, nullptr));
+            if (dyn) {
+                if (count > 0) {
+                    const Dynamics d{s.mass, s.vel, h->dt};
+                    nbody_step_kernel<128, 2, 24, false, true><<<(count + 127) / 128, 128, 0, s.dev->stream>>>(
+                        s.state[cur], h->npad, h->n, t0, count, nullptr, out, nullptr, d);
+                    HGB_LAUNCHED();
+                }
+            } else {
+                HGB_TRY(launch_step(h, s, s.state[cur], t0, count, nullptr, out, nullptr));
+            }
         }
         if (p2p) {
             // every device's next step reads what all peers stored: join the streams
@@ -269,6 +284,83 @@ int hgb_nbody_step(hgb_nbody *h, int iterations, float *ms) {
     }
     HGB_CUDA(cudaGetLastError());
     if (ms) *ms = worst;
+    return HGB_OK;
+}
+
+int hgb_nbody_step(hgb_nbody *h, int iterations, float *ms) {
+    HGB_ARG(h && iterations >= 0, "handle / iterations");
+    if (!h->uploaded) { set_error("hgb_nbody_step before hgb_nbody_upload"); return HGB_ERR_STATE; }
+    return nb_advance(h, iterations, ms, false);
+}
+
+// ---- integrator extension (the reference has positions only) -------------------
+int hgb_nbody_set_dynamics(hgb_nbody *h, const double *vel_aos, const double *mass, double dt) {
+    HGB_ARG(h, "handle");
+    HGB_ARG(dt == dt && dt - dt == 0.0, "dt must be finite");
+    for (NbShard &s : h->sh) {
+        HGB_CUDA(cudaSetDevice(s.dev->device));
+        const size_t bytes = 3ull * h->npad * sizeof(double);
+        if (!s.vel) HGB_CUDA(cudaMalloc(&s.vel, bytes));
+        if (!s.mass) HGB_CUDA(cudaMalloc(&s.mass, (size_t)h->npad * sizeof(double)));
+        if (vel_aos) {
+            HGB_CUDA(cudaMemcpyAsync(s.stage, vel_aos, 3ull * h->n * sizeof(double), cudaMemcpyHostToDevice,
+                                     s.dev->stream));
+            aos_to_soa_kernel<<<(h->npad + 255) / 256, 256, 0, s.dev->stream>>>(s.stage, s.vel, h->n, h->npad);
+            HGB_LAUNCHED();
+        } else {
+            HGB_CUDA(cudaMemsetAsync(s.vel, 0, bytes, s.dev->stream));
+        }
+        HGB_CUDA(cudaMemsetAsync(s.mass, 0, (size_t)h->npad * sizeof(double), s.dev->stream));
+        if (mass) {
+            HGB_CUDA(cudaMemcpyAsync(s.mass, mass, (size_t)h->n * sizeof(double), cudaMemcpyHostToDevice,
+                                     s.dev->stream));
+        } else {
+            fill_value_kernel<<<(h->n + 255) / 256, 256, 0, s.dev->stream>>>(s.mass, h->n, 1.0);
+            HGB_LAUNCHED();
+        }
+    }
+    for (NbShard &s : h->sh) HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
+    h->dt = dt;
+    h->dynamics = true;
+    return HGB_OK;
+}
+
+int hgb_nbody_integrate(hgb_nbody *h, int steps, float *ms) {
+    HGB_ARG(h && steps >= 0, "handle / steps");
+    if (!h->uploaded || !h->dynamics) {
+        set_error("hgb_nbody_integrate needs hgb_nbody_upload and hgb_nbody_set_dynamics first");
+        return HGB_ERR_STATE;
+    }
+    return nb_advance(h, steps, ms, true);
+}
+
+int hgb_nbody_download_velocities(hgb_nbody *h, double *vel_aos) {
+    HGB_ARG(h && vel_aos, "handle / velocities");
+    if (!h->dynamics) { set_error("no velocities: hgb_nbody_set_dynamics was not called"); return HGB_ERR_STATE; }
+    if (h->rank_mode && h->world > 1) {
+        // every rank owns one slice: gather them (in place) so each rank can return all n
+        NbShard &s = h->sh[0];
+        HGB_CUDA(cudaSetDevice(s.dev->device));
+        HGB_NCCL(nccl().GroupStart());
+        for (int c = 0; c < 3; ++c) {
+            double *recv = s.vel + (size_t)c * h->npad;
+            HGB_NCCL(nccl().AllGather(recv + (size_t)s.index * h->slice, recv, h->slice, ncclDouble,
+                                      rt().rank_comm, s.dev->stream));
+        }
+        HGB_NCCL(nccl().GroupEnd());
+    }
+    // single process: shard i holds the live velocities of slice i
+    for (NbShard &s : h->sh) {
+        HGB_CUDA(cudaSetDevice(s.dev->device));
+        const int t0 = h->rank_mode ? 0 : s.index * h->slice;
+        const int t1 = h->rank_mode ? h->n : min(h->n, t0 + h->slice);
+        if (t1 <= t0) continue;
+        soa_to_aos_kernel<<<(h->n + 255) / 256, 256, 0, s.dev->stream>>>(s.vel, s.stage, h->n, h->npad);
+        HGB_LAUNCHED();
+        HGB_CUDA(cudaMemcpyAsync(vel_aos + 3ull * t0, s.stage + 3ull * t0, 3ull * (t1 - t0) * sizeof(double),
+                                 cudaMemcpyDeviceToHost, s.dev->stream));
+    }
+    for (NbShard &s : h->sh) HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
     return HGB_OK;
 }
 
@@ -314,33 +406,61 @@ int hgb_nbody_accel_subset(hgb_nbody *h, const int *targets, int count, double *
     return HGB_OK;
 }
 
-int hgb_nbody_energy(hgb_nbody *h, double *energy) {
-    HGB_ARG(h && energy, "handle / energy");
-    if (!h->uploaded) { set_error("energy before upload"); return HGB_ERR_STATE; }
-    double total = 0.0;
-    std::vector<double> part(h->sh.size(), 0.0);
+// potential (and, with dynamics, kinetic) energy of the current state; sums per shard on the
+// device (warp shuffles + fixed-order block partials), shards added in index order on the host
+static int nb_energy(hgb_nbody *h, bool dyn, double *potential, double *kinetic) {
+    std::vector<double> part(2 * h->sh.size(), 0.0);
     for (size_t i = 0; i < h->sh.size(); ++i) {
         NbShard &s = h->sh[i];
         HGB_CUDA(cudaSetDevice(s.dev->device));
         const int t0 = s.index * h->slice;
         const int count = max(0, min(h->n, t0 + h->slice) - t0);
-        if (count == 0) continue;
         const int grid = (count + 127) / 128;
-        nbody_energy_kernel<128><<<grid, 128, 0, s.dev->stream>>>(s.state[h->cur], h->npad, h->n, t0,
-                                                                 count, s.partials + 1);
-        HGB_LAUNCHED();
-        sum_partials_kernel<<<1, 256, 0, s.dev->stream>>>(s.partials + 1, grid, s.partials);
-        HGB_LAUNCHED();
+        double *blk = s.partials + 2, *kin = blk + (h->slice / 64 + 1);
+        HGB_CUDA(cudaMemsetAsync(s.partials, 0, 2 * sizeof(double), s.dev->stream));
+        if (count > 0) {
+            if (dyn) {
+                const Dynamics d{s.mass, s.vel, h->dt};
+                nbody_energy_kernel<128, true><<<grid, 128, 0, s.dev->stream>>>(s.state[h->cur], h->npad, h->n,
+                                                                             t0, count, blk, d, kin);
+                HGB_LAUNCHED();
+                sum_partials_kernel<<<1, 256, 0, s.dev->stream>>>(kin, grid, s.partials + 1);
+                HGB_LAUNCHED();
+            } else {
+                nbody_energy_kernel<128><<<grid, 128, 0, s.dev->stream>>>(s.state[h->cur], h->npad, h->n, t0,
+                                                                         count, blk);
+                HGB_LAUNCHED();
+            }
+            sum_partials_kernel<<<1, 256, 0, s.dev->stream>>>(blk, grid, s.partials);
+            HGB_LAUNCHED();
+        }
         if (h->rank_mode && h->world > 1)
-            HGB_NCCL(nccl().AllReduce(s.partials, s.partials, 1, ncclDouble, ncclSum, rt().rank_comm,
+            HGB_NCCL(nccl().AllReduce(s.partials, s.partials, 2, ncclDouble, ncclSum, rt().rank_comm,
                                       s.dev->stream));
-        HGB_CUDA(cudaMemcpyAsync(&part[i], s.partials, sizeof(double), cudaMemcpyDeviceToHost,
+        HGB_CUDA(cudaMemcpyAsync(&part[2 * i], s.partials, 2 * sizeof(double), cudaMemcpyDeviceToHost,
                                  s.dev->stream));
     }
     for (NbShard &s : h->sh) HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
-    for (double p : part) total += p;
-    *energy = -kG * 0.5 * total;  // every pair was counted twice
+    double pot = 0.0, kin = 0.0;
+    for (size_t i = 0; i < h->sh.size(); ++i) { pot += part[2 * i]; kin += part[2 * i + 1]; }
+    *potential = -kG * 0.5 * pot;  // every pair was counted twice
+    if (kinetic) *kinetic = 0.5 * kin;
     return HGB_OK;
+}
+
+int hgb_nbody_energy(hgb_nbody *h, double *energy) {
+    HGB_ARG(h && energy, "handle / energy");
+    if (!h->uploaded) { set_error("energy before upload"); return HGB_ERR_STATE; }
+    return nb_energy(h, false, energy, nullptr);
+}
+
+int hgb_nbody_total_energy(hgb_nbody *h, double *kinetic, double *potential) {
+    HGB_ARG(h && kinetic && potential, "handle / kinetic / potential");
+    if (!h->uploaded || !h->dynamics) {
+        set_error("hgb_nbody_total_energy needs hgb_nbody_upload and hgb_nbody_set_dynamics first");
+        return HGB_ERR_STATE;
+    }
+    return nb_energy(h, true, potential, kinetic);
 }
 
 // ---- the drop-in ---------------------------------------------------------

@@ -93,6 +93,35 @@ class NBody:
         check(lib().hgb_nbody_energy(self._h, C.byref(e)))
         return e.value
 
+    # ---- integrator extension (the reference has positions only) ----
+    def set_dynamics(self, vel=None, mass=None, dt=1e-3):
+        """velocities (n,3) (None = at rest), masses (n,) (None = 1.0) and the time step of
+        integrate(): a = G sum_j m_j d f ; v += dt a ; x += dt v, every op one IEEE rounding."""
+        if vel is not None:
+            _bodies(vel, "vel")
+            assert vel.shape[0] == self.n
+        if mass is not None:
+            mass = np.ascontiguousarray(mass, dtype=np.float64)
+            assert mass.shape == (self.n,)
+        check(lib().hgb_nbody_set_dynamics(self._h, dptr(vel), dptr(mass), float(dt)))
+        return self
+
+    def integrate(self, steps=1):
+        ms = C.c_float(0.0)
+        check(lib().hgb_nbody_integrate(self._h, int(steps), C.byref(ms)))
+        return ms.value
+
+    def velocities(self):
+        vel = np.empty((self.n, 3), dtype=np.float64)
+        check(lib().hgb_nbody_download_velocities(self._h, dptr(vel)))
+        return vel
+
+    def total_energy(self):
+        """(kinetic, potential) of the current state"""
+        k, u = C.c_double(0.0), C.c_double(0.0)
+        check(lib().hgb_nbody_total_energy(self._h, C.byref(k), C.byref(u)))
+        return k.value, u.value
+
     def close(self):
         if self._h:
             lib().hgb_nbody_destroy(self._h)

@@ -87,3 +87,13 @@ def add_padding(dense, p):
     if p == 0:
         return dense.copy()
     return np.ascontiguousarray(np.pad(dense, ((0, 0), (p, p)), mode="edge"))
+
+
+def velocities(n, seed=6, scale=0.5):
+    """(n,3) velocities uniform in [-scale, scale) for the integrator extension."""
+    return ((2.0 * uniform01(seed, 3 * n) - 1.0) * scale).reshape(n, 3).copy()
+
+
+def masses(n, seed=7):
+    """(n,) masses uniform in [0.5, 1.5) / n  (total mass ~ 1)."""
+    return (0.5 + uniform01(seed, n)) / float(n)

@@ -94,6 +94,19 @@ int hgb_nbody_download(hgb_nbody *h, double *cur_aos, double *prev_aos); /* eith
 int hgb_nbody_accel_subset(hgb_nbody *h, const int *targets, int count, double *out_aos);
 /* extension, no reference counterpart: U = -G sum_{i<j} (|d|^2+EPS)^(-1/2) */
 int hgb_nbody_energy(hgb_nbody *h, double *energy);
+/* ---- nbody: integrator extension --------------------
+ * The reference moves positions only (buffer[i] = G*acc, src/nbody/nbody-run.c:22-24) and has no
+ * velocity, mass, dt or energy.  These entry points add them as a separate, clearly non-reference
+ * mode whose CPU checker is oracle_nbody_integrate (oracle/hg_oracle.c); hgb_nbody_step is unaffected.
+ * One step, per target i, sources j = 0..n-1 in order, every operation one IEEE rounding (no FMA):
+ *   a_i = G * sum_j d_ij * (m_j * f_ij)     d, s, f exactly as pair_wise_accel (:6-15)
+ *   v_i = v_i + dt * a_i ;  x_i = x_i + dt * v_i        (symplectic Euler)
+ * vel_aos: Float3D-like AoS [3n] (NULL = at rest); mass: [n] (NULL = all 1.0). */
+int hgb_nbody_set_dynamics(hgb_nbody *h, const double *vel_aos, const double *mass, double dt);
+int hgb_nbody_integrate(hgb_nbody *h, int steps, float *ms);
+int hgb_nbody_download_velocities(hgb_nbody *h, double *vel_aos);
+/* K = 1/2 sum m_i |v_i|^2,  U = -G sum_{i<j} m_i m_j (|d|^2+EPS)^(-1/2); warp-shuffle reductions */
+int hgb_nbody_total_energy(hgb_nbody *h, double *kinetic, double *potential);
 int hgb_nbody_destroy(hgb_nbody *h);
 /* pair_wise_accel(p1, p2[j], &acc) for j = 0..count-1 in order (src/nbody/nbody-run.c:6-15):
  * acc_inout[3] += d * factor, no G scaling.  Symbol-level drop-in, one GPU thread. */

@@ -204,3 +204,73 @@ double oracle_nbody_energy(const double *pos, int n, int threads) {
     }
     return (double)(-(long double)HG_G * total);
 }
+
+/* ---- integrator extension -------------------------------------------
+ * The reference has positions only; this is the CPU checker for hgb_nbody_integrate /
+ * hgb_nbody_total_energy (include/hgb200.h).  The pairwise part is pair_wise_accel
+ * (src/nbody/nbody-run.c:6-15) with the factor weighted by the source mass; every operator
+ * is one IEEE binary64 operation, sources in index order, self pair included. */
+static void oracle_accel_mass(const double *pos, const double *mass, int index, int n, double *a) {
+    const double px = pos[3 * index + 0], py = pos[3 * index + 1], pz = pos[3 * index + 2];
+    double ax = 0.0, ay = 0.0, az = 0.0;
+    for (int j = 0; j < n; ++j) {
+        double dx = pos[3 * j + 0] - px;
+        double dy = pos[3 * j + 1] - py;
+        double dz = pos[3 * j + 2] - pz;
+        double s = dx * dx + dy * dy + dz * dz + HG_EPS;
+        double f = 1.0 / sqrt(s * s * s);
+        double w = mass[j] * f;
+        ax += dx * w;
+        ay += dy * w;
+        az += dz * w;
+    }
+    a[0] = HG_G * ax;
+    a[1] = HG_G * ay;
+    a[2] = HG_G * az;
+}
+
+/* `steps` x { a = accel(pos); vel += dt*a; pos += dt*vel } (symplectic Euler), in place. */
+void oracle_nbody_integrate(double *pos, double *vel, const double *mass, int n, double dt, int steps,
+                            int threads, double *scratch /* 3n doubles */) {
+    if (threads < 1) threads = 1;
+    for (int it = 0; it < steps; ++it) {
+#pragma omp parallel for num_threads(threads) schedule(static)
+        for (int i = 0; i < n; ++i) {
+            double a[3];
+            oracle_accel_mass(pos, mass, i, n, a);
+            for (int c = 0; c < 3; ++c) {
+                double t = dt * a[c];
+                double v = vel[3 * i + c] + t;
+                vel[3 * i + c] = v;
+                double u = dt * v;
+                scratch[3 * i + c] = pos[3 * i + c] + u;
+            }
+        }
+        memcpy(pos, scratch, (size_t)n * 3 * sizeof(double));
+    }
+}
+
+/* K = 1/2 sum m v^2 and U = -G sum_{i<j} m_i m_j / sqrt(|d|^2+EPS), both in long double. */
+void oracle_nbody_total_energy(const double *pos, const double *vel, const double *mass, int n,
+                               int threads, double *kinetic, double *potential) {
+    long double k = 0.0L, u = 0.0L;
+    if (threads < 1) threads = 1;
+#pragma omp parallel for num_threads(threads) schedule(dynamic, 64) reduction(+ : k, u)
+    for (int i = 0; i < n; ++i) {
+        long double acc = 0.0L;
+        for (int j = i + 1; j < n; ++j) {
+            double dx = pos[3 * j + 0] - pos[3 * i + 0];
+            double dy = pos[3 * j + 1] - pos[3 * i + 1];
+            double dz = pos[3 * j + 2] - pos[3 * i + 2];
+            long double s = (long double)dx * dx + (long double)dy * dy + (long double)dz * dz +
+                            (long double)HG_EPS;
+            acc += (long double)mass[j] / sqrtl(s);
+        }
+        u += (long double)mass[i] * acc;
+        k += (long double)mass[i] * ((long double)vel[3 * i] * vel[3 * i] +
+                                     (long double)vel[3 * i + 1] * vel[3 * i + 1] +
+                                     (long double)vel[3 * i + 2] * vel[3 * i + 2]);
+    }
+    *kinetic = (double)(0.5L * k);
+    *potential = (double)(-(long double)HG_G * u);
+}

@@ -36,6 +36,8 @@ def lib():
         L.oracle_fill_planets.argtypes = [_dp, C.c_int]
         L.oracle_nbody_energy.argtypes = [_dp, C.c_int, C.c_int]
         L.oracle_nbody_energy.restype = C.c_double
+        L.oracle_nbody_integrate.argtypes = [_dp, _dp, _dp, C.c_int, C.c_double, C.c_int, C.c_int, _dp]
+        L.oracle_nbody_total_energy.argtypes = [_dp, _dp, _dp, C.c_int, C.c_int, _dp, _dp]
         _LIB = L
     return _LIB
 
@@ -105,3 +107,17 @@ def fill_planets(n):
 
 def nbody_energy(pos, threads=None):
     return lib().oracle_nbody_energy(_p(pos), pos.shape[0], threads or ncpu())
+
+
+def nbody_integrate(pos, vel, mass, dt, steps, threads=None):
+    """Integrator extension (no reference counterpart): pos, vel advanced in place."""
+    scratch = np.empty_like(pos)
+    lib().oracle_nbody_integrate(_p(pos), _p(vel), _p(mass), pos.shape[0], float(dt), int(steps),
+                                 threads or ncpu(), _p(scratch))
+
+
+def nbody_total_energy(pos, vel, mass, threads=None):
+    k, u = C.c_double(0.0), C.c_double(0.0)
+    lib().oracle_nbody_total_energy(_p(pos), _p(vel), _p(mass), pos.shape[0], threads or ncpu(),
+                                    C.byref(k), C.byref(u))
+    return k.value, u.value

@@ -231,3 +231,49 @@ def test_conv_port_equals_reference_binary():
 def test_golden_fixture_is_the_shipped_file(shipped_image):
     img = ref.read_image("/root/reference/2d-convolution.input")
     assert np.array_equal(img, shipped_image)
+
+
+# ---- integrator extension: pinned to the reference through the unit-mass case ----
+def test_integrator_unit_mass_kick_is_the_reference_accel():
+    """mass = 1, at rest, dt = 1: the new velocity is exactly what the reference's run() writes
+    (buffer[i] = G*acc, src/nbody/nbody-run.c:22-24), and x' = x + v'."""
+    n = 700
+    pos = synth.plummer(n, seed=9)
+    a, b = pos.copy(), np.zeros_like(pos)
+    port.nbody_run(a, b, 1)                          # b = accel of state 0 (pinned to the reference)
+    p, v = pos.copy(), np.zeros_like(pos)
+    port.nbody_integrate(p, v, np.ones(n), 1.0, 1)
+    assert np.array_equal(v, b)
+    assert np.array_equal(p, pos + b)
+
+
+def test_integrator_matches_a_numpy_restatement():
+    n, dt, steps = 97, 0.01, 4
+    pos, vel, mass = synth.plummer(n, seed=3), synth.velocities(n, seed=4), synth.masses(n, seed=5)
+    p, v = pos.copy(), vel.copy()
+    port.nbody_integrate(p, v, mass, dt, steps, threads=3)
+    q, w = pos.copy(), vel.copy()
+    for _ in range(steps):
+        acc = np.zeros_like(q)
+        for j in range(n):                           # sources in order: one rounding per operation
+            d = q[j] - q
+            s = d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1] + d[:, 2] * d[:, 2] + 0.005
+            f = mass[j] * (1.0 / np.sqrt(s * s * s))
+            acc += d * f[:, None]
+        w = w + dt * (9.8 * acc)
+        q = q + dt * w
+    assert np.array_equal(p, q) and np.array_equal(v, w)
+
+
+def test_integrator_energy_is_conserved_and_threads_do_not_matter():
+    n = 300
+    pos, vel, mass = synth.plummer(n, seed=3), synth.velocities(n, seed=4, scale=0.05), synth.masses(n, seed=5)
+    k0, u0 = port.nbody_total_energy(pos, vel, mass)
+    p1, v1 = pos.copy(), vel.copy()
+    port.nbody_integrate(p1, v1, mass, 1e-3, 50, threads=1)
+    p2, v2 = pos.copy(), vel.copy()
+    port.nbody_integrate(p2, v2, mass, 1e-3, 50, threads=4)
+    assert np.array_equal(p1, p2) and np.array_equal(v1, v2)
+    k1, u1 = port.nbody_total_energy(p1, v1, mass)
+    assert abs((k1 + u1) - (k0 + u0)) <= 1e-3 * abs(k0 + u0)
+    assert k0 > 0 and u0 < 0
