@@ -85,6 +85,20 @@ class ClockSampler:
                 "samples": len(sm), "power_w_max": max(pw) if pw else None}
 
 
+def ncu_traffic(kernel_prefix):
+    """DRAM bytes per launch of a kernel from the committed ncu --set full capture
+    (profiles/ncu_traffic.json, written by tools/ncu_summary.py --traffic); None if absent."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            table = json.load(f)
+    except (OSError, ValueError):
+        return None
+    for name, row in table.items():
+        if name.startswith(kernel_prefix):
+            return row["dram_bytes_per_launch"]
+    return None
+
+
 def pinned(shape):
     """numpy array backed by pinned host memory (the e2e legs copy from/to pinned buffers)"""
     import torch
@@ -312,7 +326,9 @@ def main():
                      "roofline": {"bound": "hbm", "achieved": gbps / world, "peak": peaks.get("hbm_gbs", 6650.0),
                                   "unit": "GB/s", "frac": gbps / world / peaks.get("hbm_gbs", 6650.0),
                                   "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if "hbm_gbs" in peaks else "fallback 6650 (of fallback)",
-                                  "traffic": None, "per_gpu": True}}
+                                  "traffic": ncu_traffic(f"conv_stream_kernel<{k},"),
+                                  "traffic_note": f"ncu dram bytes per launch at 16384^2 on 1 GPU (profiles/ncu_traffic.json); algorithmic {cn * cn * BYTES_PER_PIXEL} B",
+                                  "per_gpu": True}}
             if k >= 5:   # 2*K^2 unfused FP64 ops per pixel make 5x5/7x7 FP64-pipe bound
                 ops = 2.0 * k * k * cn * cn * CONV_TIMED / (ms * 1e-3) / world
                 entry["roofline_fp64"] = {"bound": "fp64", "achieved": ops / 1e12, "peak": tf.value / 2,
@@ -340,7 +356,9 @@ def main():
             "clocks": clocks,
             "roofline": {"bound": "fp64", "achieved": value / world * FLOP_PER_INTERACTION / 1e12, "peak": tf.value,
                          "unit": "TFLOP/s", "frac": value / world * FLOP_PER_INTERACTION / 1e12 / tf.value,
-                         "traffic": None, "per_gpu": True,
+                         "traffic": ncu_traffic("nbody_step_kernel<"),
+                         "traffic_note": "ncu dram bytes per launch (profiles/ncu_traffic.json): the 24 MiB of positions stay in L2",
+                         "per_gpu": True,
                          "peak_source": "in-run dependent-free DFMA probe (MEASURED_PEAKS.json has no FP64 figure)",
                          "fp64_pipe_util": value / world * FP64_INSTR_PER_INTERACTION / (tf.value / 2 * 1e12),
                          "fp64_pipe_util_note": f"{FP64_INSTR_PER_INTERACTION} FP64-pipe instructions per interaction in exact mode (SASS count) vs measured DFMA issue rate",

@@ -68,8 +68,17 @@ SIGNATURES = {
     "hgb_conv_upload": (C.c_int, [_vp, _dp]),
     "hgb_conv_step": (C.c_int, [_vp, C.c_int, _fp]),
     "hgb_conv_download": (C.c_int, [_vp, _dp, _dp]),
+    "hgb_conv_upload_dense": (C.c_int, [_vp, _dp]),
+    "hgb_conv_download_dense": (C.c_int, [_vp, _dp]),
+    "hgb_conv_backup": (C.c_int, [_vp]),
+    "hgb_conv_restore": (C.c_int, [_vp]),
     "hgb_conv_checksum": (C.c_int, [_vp, _dp]),
     "hgb_conv_destroy": (C.c_int, [_vp]),
+    "hgb_image_read_text": (C.c_int, [C.c_char_p, _ip, _ip, C.POINTER(_dp)]),
+    "hgb_image_write_text": (C.c_int, [C.c_char_p, _dp, C.c_int, C.c_int]),
+    "hgb_image_read_binary": (C.c_int, [C.c_char_p, _ip, _ip, C.POINTER(_dp)]),
+    "hgb_image_write_binary": (C.c_int, [C.c_char_p, _dp, C.c_int, C.c_int]),
+    "hgb_image_free": (None, [_dp]),
 }
 
 _LIB = None

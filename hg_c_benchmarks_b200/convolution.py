@@ -113,6 +113,38 @@ def get_checksum(img):
     return val
 
 
+def _read(fn, path):
+    w, h, data = C.c_int(), C.c_int(), C.POINTER(C.c_double)()
+    check(fn(str(path).encode(), C.byref(w), C.byref(h), C.byref(data)))
+    try:
+        img = Image(w.value, h.value)
+        img.image[...] = np.ctypeslib.as_array(data, shape=(h.value, w.value))
+    finally:
+        lib().hgb_image_free(data)
+    return img
+
+
+def read_image(path):
+    """read_image_from_fd (convolution-util.c:9-45): "<height> <width>" then one line per row.
+    Same token rules as the reference, no 16384-byte line limit; errors raise instead of exit(2)."""
+    return _read(lib().hgb_image_read_text, path)
+
+
+def write_image(path, img):
+    check(lib().hgb_image_write_text(str(path).encode(), dptr(np.ascontiguousarray(img.image)), img.width,
+                                     img.height))
+
+
+def read_image_binary(path):
+    """HGBIMG1: magic, int32 height, int32 width, raw little-endian doubles (for 16k x 16k images)"""
+    return _read(lib().hgb_image_read_binary, path)
+
+
+def write_image_binary(path, img):
+    check(lib().hgb_image_write_binary(str(path).encode(), dptr(np.ascontiguousarray(img.image)), img.width,
+                                       img.height))
+
+
 def get_default_kernel():
     """convolution-util.c:135-151"""
     k = Image(5, 5, 0.0)
@@ -211,6 +243,31 @@ class Conv2D:
         prev = np.empty(shape, dtype=np.float64) if want_prev else None
         check(lib().hgb_conv_download(self._h, dptr(cur), dptr(prev)))
         return (cur, prev) if want_prev else cur
+
+    # ---- device-resident lifecycle (reference src/2d-convolution.c:41-74 without host round trips) ----
+    def upload_dense(self, dense):
+        """add_padding on the device: dense is the unpadded (band rows, w) image"""
+        assert dense.shape == (self.band()[1], self.w), dense.shape
+        check(lib().hgb_conv_upload_dense(self._h, dptr(dense)))
+        return self
+
+    def download_dense(self, out=None):
+        """remove_padding of the newest state"""
+        shape = (self.band()[1], self.w)
+        dense = np.empty(shape, dtype=np.float64) if out is None else out
+        assert dense.shape == shape
+        check(lib().hgb_conv_download_dense(self._h, dptr(dense)))
+        return dense
+
+    def backup(self):
+        """copy_padded_image(img, backup), device to device"""
+        check(lib().hgb_conv_backup(self._h))
+        return self
+
+    def restore(self):
+        """copy_padded_image(backup, img), device to device"""
+        check(lib().hgb_conv_restore(self._h))
+        return self
 
     def checksum(self):
         c = C.c_double(0.0)

@@ -199,6 +199,19 @@ conv_stream_kernel(const double *__restrict__ in, double *__restrict__ out, Band
 // not needed: pad columns travel with the rows (full pitch) in every copy.
 
 // sequential row-major checksum (reference get_checksum, convolution-util.c:63-71):
+// add_padding's pad columns (reference src/convolution/convolution-util.c:258-269 via
+// init_padded_image/update_borders): for stored rows [r0, r1) of the band (halo rows included)
+// copy inner pixel 0 into the p columns left of it and pixel W-1 into the p columns right of it.
+__global__ void __launch_bounds__(128)
+conv_pad_columns_kernel(double *__restrict__ img, BandGeom g, int r0, int r1) {
+    const int y = r0 + blockIdx.x * (blockDim.x / 8) + threadIdx.x / 8;
+    const int i = threadIdx.x % 8;          // p <= 7 for the specialised kernels; loop covers more
+    if (y >= r1) return;
+    double *row = img + band_row_off(g, y) + kLead;
+    const double left = row[0], right = row[g.W - 1];
+    for (int q = i; q < g.p; q += 8) { row[-1 - q] = left; row[g.W + q] = right; }
+}
+
 // one warp stages 32 doubles at a time, lane 0 adds them in order.  Exact but
 // serial; used by tests and the CLI path only.
 __global__ void __launch_bounds__(32)

@@ -16,6 +16,7 @@ struct CvShard {
     double *img[2] = {nullptr, nullptr};
     double *taps_dev = nullptr;
     double *scratch = nullptr;
+    double *bak = nullptr;       // hgb_conv_backup: copy of one state (copy_padded_image on the device)
 };
 }  // namespace
 
@@ -33,6 +34,8 @@ struct hgb_conv {
     bool overlap = true;   // boundary/interior split with the exchange under the interior kernel
     int cur = 0;
     bool uploaded = false;
+    bool have_backup = false;
+    int bak_valid_xr = 0;
     std::vector<CvShard> sh;
 };
 
@@ -215,6 +218,7 @@ int hgb_conv_destroy(hgb_conv *h) {
         cudaFree(s.img[1]);
         cudaFree(s.taps_dev);
         cudaFree(s.scratch);
+        if (s.bak) cudaFree(s.bak);
     }
     delete h;
     return HGB_OK;
@@ -455,6 +459,87 @@ int hgb_conv_download(hgb_conv *h, double *cur, double *prev) {
         }
     }
     for (CvShard &s : h->sh) HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
+    return HGB_OK;
+}
+
+// ---- device-resident image lifecycle ---------------------------------------
+// add_padding (reference src/convolution/convolution-util.c:258-269) on the device: `dense` is the
+// unpadded image, inner_h rows of inner_w doubles (rank mode: this rank's band of it); the pad
+// columns are produced here instead of being marshalled from the host.
+int hgb_conv_upload_dense(hgb_conv *h, const double *dense) {
+    HGB_ARG(h && dense, "handle / image");
+    const size_t w = (size_t)h->W;
+    for (CvShard &s : h->sh) {
+        if (s.rows <= 0) continue;
+        HGB_CUDA(cudaSetDevice(s.dev->device));
+        int g0 = s.row0, g1 = s.row0 + s.rows;
+        const double *src = dense;
+        if (!h->rank_mode) {
+            g0 = max(0, s.row0 - h->halo);
+            g1 = min(h->H, s.row0 + s.rows + h->halo);
+            src = dense + (size_t)g0 * w;
+        }
+        double *dst = s.img[0] + (size_t)(g0 - s.row0 + h->halo) * h->dp + kLead;
+        HGB_CUDA(cudaMemcpy2DAsync(dst, h->dp * sizeof(double), src, w * sizeof(double), w * sizeof(double),
+                                   g1 - g0, cudaMemcpyHostToDevice, s.dev->stream));
+        if (h->p > 0) {
+            conv_pad_columns_kernel<<<(g1 - g0 + 15) / 16, 128, 0, s.dev->stream>>>(s.img[0], geom(h, s), g0, g1);
+            HGB_LAUNCHED();
+        }
+    }
+    h->cur = 0;
+    h->uploaded = true;
+    h->valid_xr = h->rank_mode ? 0 : h->halo;
+    if (h->rank_mode && h->world > 1) HGB_TRY(halo_exchange(h, 0));
+    for (CvShard &s : h->sh) HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
+    return HGB_OK;
+}
+
+// remove_padding (reference src/convolution/convolution-util.c:271-279) of the newest state
+int hgb_conv_download_dense(hgb_conv *h, double *dense) {
+    HGB_ARG(h && dense, "handle / image");
+    if (!h->uploaded) { set_error("hgb_conv_download_dense before upload"); return HGB_ERR_STATE; }
+    const size_t w = (size_t)h->W;
+    for (CvShard &s : h->sh) {
+        if (s.rows <= 0) continue;
+        HGB_CUDA(cudaSetDevice(s.dev->device));
+        double *dst = dense + (h->rank_mode ? 0 : (size_t)s.row0 * w);
+        const double *src = s.img[h->cur] + (size_t)h->halo * h->dp + kLead;
+        HGB_CUDA(cudaMemcpy2DAsync(dst, w * sizeof(double), src, h->dp * sizeof(double), w * sizeof(double),
+                                   s.rows, cudaMemcpyDeviceToHost, s.dev->stream));
+    }
+    for (CvShard &s : h->sh) HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
+    return HGB_OK;
+}
+
+// copy_padded_image(img, backup) / copy_padded_image(backup, img) (reference
+// src/convolution/convolution-util.c:357-373, the REPETITION loop of src/2d-convolution.c:63-68)
+// as device-to-device copies: the newest state is saved, restore makes it the newest state again.
+int hgb_conv_backup(hgb_conv *h) {
+    HGB_ARG(h, "handle");
+    if (!h->uploaded) { set_error("hgb_conv_backup before upload"); return HGB_ERR_STATE; }
+    for (CvShard &s : h->sh) {
+        HGB_CUDA(cudaSetDevice(s.dev->device));
+        const size_t bytes = (size_t)(s.rows + 2 * h->halo + 1) * h->dp * sizeof(double);
+        if (!s.bak) HGB_CUDA(cudaMalloc(&s.bak, bytes));
+        HGB_CUDA(cudaMemcpyAsync(s.bak, s.img[h->cur], bytes, cudaMemcpyDeviceToDevice, s.dev->stream));
+    }
+    for (CvShard &s : h->sh) HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
+    h->have_backup = true;
+    h->bak_valid_xr = h->valid_xr;
+    return HGB_OK;
+}
+
+int hgb_conv_restore(hgb_conv *h) {
+    HGB_ARG(h, "handle");
+    if (!h->have_backup) { set_error("hgb_conv_restore without hgb_conv_backup"); return HGB_ERR_STATE; }
+    for (CvShard &s : h->sh) {
+        HGB_CUDA(cudaSetDevice(s.dev->device));
+        const size_t bytes = (size_t)(s.rows + 2 * h->halo + 1) * h->dp * sizeof(double);
+        HGB_CUDA(cudaMemcpyAsync(s.img[h->cur], s.bak, bytes, cudaMemcpyDeviceToDevice, s.dev->stream));
+    }
+    for (CvShard &s : h->sh) HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
+    h->valid_xr = h->bak_valid_xr;
     return HGB_OK;
 }
 

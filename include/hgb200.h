@@ -154,9 +154,32 @@ int hgb_conv_band(hgb_conv *h, int *row0, int *rows);
 int hgb_conv_upload(hgb_conv *h, const double *cur);
 int hgb_conv_step(hgb_conv *h, int iterations, float *ms);
 int hgb_conv_download(hgb_conv *h, double *cur, double *prev /* either may be NULL */);
+/* device-resident image lifecycle -- what src/2d-convolution.c:41-74 does with
+ * add_padding / copy_padded_image / remove_padding around the benchmark, without the host round trips:
+ * upload_dense = add_padding (convolution-util.c:258-269): `dense` is inner_h rows of inner_w doubles
+ * (rank mode: this rank's band), pad columns are produced on the device;
+ * download_dense = remove_padding (:271-279) of the newest state;
+ * backup / restore = copy_padded_image (:357-373) to and from a device-side copy of the newest state. */
+int hgb_conv_upload_dense(hgb_conv *h, const double *dense);
+int hgb_conv_download_dense(hgb_conv *h, double *dense);
+int hgb_conv_backup(hgb_conv *h);
+int hgb_conv_restore(hgb_conv *h);
 /* get_checksum(remove_padding(img)) (convolution-util.c:63-71): sequential row-major sum */
 int hgb_conv_checksum(hgb_conv *h, double *checksum);
 int hgb_conv_destroy(hgb_conv *h);
+
+/* ---- convolution: image files (host code, no GPU needed) ----
+ * Text = the reference's format (read_image_from_fd, src/convolution/convolution-util.c:9-45;
+ * 2d-convolution.input, kernel.txt, laplace.txt): "<height> <width>" -- height FIRST, as the code
+ * reads it -- then one space-separated line per row; same strtok/strtol/strtod token rules, but no
+ * 16384-byte line limit, and errors are returned where the reference calls bail_out.
+ * Binary = "HGBIMG1\n", int32 height, int32 width, height*width little-endian doubles.
+ * *data is malloc'ed by the library: release it with hgb_image_free. */
+int hgb_image_read_text(const char *path, int *width, int *height, double **data);
+int hgb_image_write_text(const char *path, const double *data, int width, int height);
+int hgb_image_read_binary(const char *path, int *width, int *height, double **data);
+int hgb_image_write_binary(const char *path, const double *data, int width, int height);
+void hgb_image_free(double *data);
 
 #ifdef __cplusplus
 }

@@ -1,6 +1,7 @@
 """Summarise an .ncu-rep (read here, no GPU needed) into a small text file for profiles/.
 usage: python tools/ncu_summary.py gpurun_out/prof.ncu-rep profiles/out.txt"""
 import csv
+import os
 import subprocess
 import sys
 
@@ -20,6 +21,27 @@ KEEP = [
     "smsp__warps_eligible.avg.per_cycle_active",
 ]
 STALL = "smsp__average_warps_issue_stalled_"
+
+
+def traffic_json(reps, out):
+    """per-kernel DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum, mean over the captured
+    launches) -> profiles/ncu_traffic.json, which bench.py quotes as roofline.traffic"""
+    import json
+    scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    acc = {}
+    for rep in reps:
+        raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+        rows = list(csv.reader(l for l in raw.splitlines() if l.startswith('"')))
+        hdr, units = rows[0], rows[1]
+        ir, iw, ik = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum"), hdr.index("Kernel Name")
+        for r in rows[2:]:
+            name = r[ik].split("(")[0].replace("void ", "").replace("hgb::", "").strip()
+            acc.setdefault(name, []).append(float(r[ir]) * scale[units[ir]] + float(r[iw]) * scale[units[iw]])
+    res = {k: {"dram_bytes_per_launch": sum(v) / len(v), "launches": len(v)} for k, v in acc.items()}
+    res["_source"] = "ncu --set full --clock-control none: " + ", ".join(os.path.basename(r) for r in reps)
+    with open(out, "w") as f:
+        json.dump(res, f, indent=1, sort_keys=True)
+        f.write("\n")
 
 
 def main(rep, out):
@@ -56,4 +78,7 @@ def main(rep, out):
 
 
 if __name__ == "__main__":
-    main(sys.argv[1], sys.argv[2])
+    if sys.argv[1] == "--traffic":      # python tools/ncu_summary.py --traffic out.json rep1 rep2 ...
+        traffic_json(sys.argv[3:], sys.argv[2])
+    else:
+        main(sys.argv[1], sys.argv[2])
