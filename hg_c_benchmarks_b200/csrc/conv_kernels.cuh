@@ -195,10 +195,173 @@ conv_stream_kernel(const double *__restrict__ in, double *__restrict__ out, Band
     }
 }
 
-// pad-column refresh for the rows a rank receives or for freshly uploaded data is
-// not needed: pad columns travel with the rows (full pitch) in every copy.
+// ---- 3x3: two iterations per pass (temporal blocking) -----------------------
+// The 3x3 stencil is HBM-bound (16 B and 18 FP64 ops per pixel), so a pass that applies the
+// kernel TWICE halves the DRAM traffic per iteration.  A CTA streams input rows y0-2 .. y0+n+1 of
+// a strip through a shared-memory ring (bulk copies, one mbarrier per row); stage 1 turns them
+// into rows of the intermediate state (iteration t+1), which live only in a two-row shared-memory
+// buffer; stage 2 consumes each intermediate row at once and emits rows of iteration t+2.  Both
+// stages keep 3x2 running sums per thread in registers and apply the taps in the reference's
+// row-major order with one __dmul_rn + one __dadd_rn each, so every value -- intermediate and
+// final -- is bit-identical to two separate passes.  update_borders between the two iterations
+// (pad columns = edge pixels) and the aliased pad rows (row index clamp) are applied to the
+// intermediate state on the fly:
+//   * columns: a strip computes 256 intermediate columns xs .. xs+255 and outputs the 254 inside
+//     them; an intermediate column left of 0 / right of W-1 is replaced by column 0 / W-1;
+//   * rows: intermediate row -1 / H would alias row 0 / H-1, so output row 0 takes its first tap
+//     row from intermediate row 0 as well, and output row H-1 its last one from row H-1.
+constexpr int kF2TW = 256;              // intermediate columns per CTA
+constexpr int kF2Out = kF2TW - 2;       // output columns per CTA
+constexpr int kF2Pitch = kF2TW + 4;     // shared-memory row pitch (doubles): 16-byte multiple, room for +2/+3 reads
+constexpr int kF2Ring = 6;              // input rows in flight: two halves of three (the loop is unrolled by 3)
+constexpr int kF2Threads = kF2TW / 2;
+constexpr size_t kF2Smem = (size_t)(kF2Ring + 2) * kF2Pitch * sizeof(double) + kF2Ring * sizeof(uint64_t);
 
-// sequential row-major checksum (reference get_checksum, convolution-util.c:63-71):
+__global__ void __launch_bounds__(kF2Threads)
+conv3_fused2_kernel(const double *__restrict__ in, double *__restrict__ out, BandGeom g, int chunk,
+                    const __grid_constant__ Taps taps) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    double *inring = reinterpret_cast<double *>(smem_raw);
+    double *mid = inring + kF2Ring * kF2Pitch;
+    uint64_t *full = reinterpret_cast<uint64_t *>(mid + 2 * kF2Pitch);
+
+    const int xs = blockIdx.x * kF2Out - 1;                      // first intermediate column
+    const int y0 = g.crow0 + blockIdx.y * chunk;                 // first output row (global)
+    const int nrows = min(chunk, g.crow0 + g.crows - y0);
+    const int nin = nrows + 4;                                   // input rows y0-2 .. y0+nrows+1
+    const int tid = threadIdx.x;
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < kF2Ring; ++s) mbar_init(&full[s], 1);
+        mbar_init_fence();
+    }
+    __syncthreads();
+
+    // thread 0: input row i of the chunk into ring slot `slot` (= i % 6)
+    const double *in_strip = in + kLead + (xs - 1);              // even column: 16-byte aligned
+    auto issue = [&](int i, int slot) {
+        const int gr = min(max(y0 - 2 + i, 0), g.H - 1);         // aliased pad rows == clamp
+        mbar_expect_tx(&full[slot], (uint32_t)((kF2TW + 2) * sizeof(double)));
+        bulk_g2s(inring + slot * kF2Pitch, in_strip + band_row_off(g, gr), (kF2TW + 2) * sizeof(double),
+                 &full[slot]);
+    };
+    if (tid == 0)
+        for (int i = 0; i < kF2Ring && i < nin; ++i) issue(i, i);
+
+    const int a = xs + 2 * tid;            // global column of this thread's first intermediate value
+    const int c0 = a + 1;                  // first of its two output columns
+    const bool has_out = tid < kF2Threads - 1 && c0 < g.W;
+    const bool st_pair = has_out && c0 + 1 < g.W;                // double2 store, else one column
+    const bool pad_left = has_out && c0 == 0;                    // update_borders of the output
+    const int pad_right = !has_out ? -1 : c0 == g.W - 1 ? 0 : c0 + 1 == g.W - 1 ? 1 : -1;
+    const bool edge_strip = blockIdx.x == 0 || xs + kF2TW + 2 > g.W;
+    const int last = g.W - 1 - a;          // position of column W-1 among this thread's 4 intermediate values
+    // chunks that hold image row 0 or H-1 take the variant of stage 2 with the row-alias rules
+    const bool edge_rows = y0 == 0 || y0 + nrows >= g.H;
+    double *const out_col = out + band_row_off(g, y0) + kLead + c0;
+
+    double a1[3][2], a2[3][2];
+#pragma unroll
+    for (int q = 0; q < 3; ++q) { a1[q][0] = a1[q][1] = 0.0; a2[q][0] = a2[q][1] = 0.0; }
+
+    auto store_row = [&](int o, double v0, double v1) {
+        double *orow = out_col + (size_t)o * g.dp;
+        if (st_pair) *reinterpret_cast<double2 *>(orow) = make_double2(v0, v1);
+        else orow[0] = v0;
+        if (pad_left) orow[-1] = v0;
+        if (pad_right == 0) orow[1] = v0;
+        if (pad_right == 1) orow[2] = v1;
+    };
+
+    for (int k = 0, i0 = 0; i0 < nin; ++k, i0 += 3) {
+        const int half = k & 1;                                  // ring slot of phase ph is 3*half + ph
+        const uint32_t parity = (uint32_t)(k >> 1) & 1u;
+        const double *in_half = inring + half * 3 * kF2Pitch + 2 * tid;
+        double *mid_a = mid + half * kF2Pitch + 2 * tid;         // intermediate row j lives in slot j & 1 == (k + ph) & 1
+        double *mid_b = mid + (half ^ 1) * kF2Pitch + 2 * tid;
+#pragma unroll
+        for (int ph = 0; ph < 3; ++ph) {
+            const int i = i0 + ph;
+            if (i >= nin) break;
+            mbar_wait(&full[3 * half + ph], parity);
+            {   // stage 1: input row i feeds the intermediate rows it is the top / middle / bottom row of
+                const double *srow = in_half + ph * kF2Pitch;
+                const double2 p0 = *reinterpret_cast<const double2 *>(srow);
+                const double2 p1 = *reinterpret_cast<const double2 *>(srow + 2);
+                const double v[4] = {p0.x, p0.y, p1.x, p1.y};    // input columns a-1 .. a+2
+#pragma unroll
+                for (int ky = 0; ky < 3; ++ky) {
+                    const int sl = (ph - ky + 3) % 3;
+#pragma unroll
+                    for (int c = 0; c < 2; ++c) {
+                        double val = (ky == 0) ? 0.0 : a1[sl][c];
+#pragma unroll
+                        for (int kx = 0; kx < 3; ++kx) val = __dadd_rn(val, __dmul_rn(taps.k[ky * 3 + kx], v[c + kx]));
+                        a1[sl][c] = val;
+                    }
+                }
+            }
+            // intermediate row j = i-2 (global row y0-1+j) is complete in accumulator slot (ph+1)%3
+            const int j = i - 2;
+            double *mrow = (ph == 1) ? mid_b : mid_a;
+            if (j >= 0) *reinterpret_cast<double2 *>(mrow) = make_double2(a1[(ph + 1) % 3][0], a1[(ph + 1) % 3][1]);
+            __syncthreads();               // intermediate row visible; input slot drained by everyone
+            if (tid == 0 && i + kF2Ring < nin) issue(i + kF2Ring, 3 * half + ph);
+            if (j < 0) continue;
+            // stage 2: intermediate row j feeds output rows j, j-1, j-2 (relative to y0)
+            const double2 q0 = *reinterpret_cast<const double2 *>(mrow);
+            const double2 q1 = *reinterpret_cast<const double2 *>(mrow + 2);
+            double w[4] = {q0.x, q0.y, q1.x, q1.y};              // intermediate columns a .. a+3
+            if (edge_strip) {              // update_borders of the intermediate state
+                if (a < 0) w[0] = w[1];
+                if (last >= 0 && last < 3) {
+                    const double wl = last == 0 ? w[0] : last == 1 ? w[1] : w[2];
+                    if (last < 1) w[1] = wl;
+                    if (last < 2) w[2] = wl;
+                    w[3] = wl;
+                }
+            }
+            auto stage2 = [&](auto edge_tag) {
+                constexpr bool EDGE = decltype(edge_tag)::value;
+#pragma unroll
+                for (int ky = 0; ky < 3; ++ky) {
+                    const int sl = (ph + 1 - ky + 3) % 3;
+                    const int o = j - ky;                        // output row relative to y0
+                    const bool top = EDGE && ky == 1 && y0 + o == 0;            // warp-uniform
+                    const bool bottom = EDGE && ky == 1 && y0 + o == g.H - 1;
+#pragma unroll
+                    for (int c = 0; c < 2; ++c) {
+                        double val = (ky == 0) ? 0.0 : a2[sl][c];
+                        if (EDGE && top) { // intermediate row -1 aliases row 0: tap row 0 comes from this row too
+                            val = 0.0;
+#pragma unroll
+                            for (int kx = 0; kx < 3; ++kx) val = __dadd_rn(val, __dmul_rn(taps.k[kx], w[c + kx]));
+                        }
+#pragma unroll
+                        for (int kx = 0; kx < 3; ++kx) val = __dadd_rn(val, __dmul_rn(taps.k[ky * 3 + kx], w[c + kx]));
+                        if (EDGE && bottom) {   // intermediate row H aliases row H-1: tap row 2 from this row as well
+#pragma unroll
+                            for (int kx = 0; kx < 3; ++kx) val = __dadd_rn(val, __dmul_rn(taps.k[6 + kx], w[c + kx]));
+                        }
+                        a2[sl][c] = val;
+                    }
+                    if (EDGE) {
+                        const bool done = (ky == 2 && y0 + o != g.H - 1) || bottom;
+                        if (done && o >= 0 && o < nrows && has_out) store_row(o, a2[sl][0], a2[sl][1]);
+                    } else {
+                        if (ky == 2 && o >= 0 && has_out) store_row(o, a2[sl][0], a2[sl][1]);   // o < nrows: i < nin
+                    }
+                }
+            };
+            if (edge_rows) stage2(std::true_type{});
+            else stage2(std::false_type{});
+        }
+    }
+}
+
+// sequential row-major checksum (reference get_checksum, convolution-util.c:63-71): see
+// conv_checksum_seq_kernel below.
 // add_padding's pad columns (reference src/convolution/convolution-util.c:258-269 via
 // init_padded_image/update_borders): for stored rows [r0, r1) of the band (halo rows included)
 // copy inner pixel 0 into the p columns left of it and pixel W-1 into the p columns right of it.

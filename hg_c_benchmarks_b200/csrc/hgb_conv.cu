@@ -32,6 +32,7 @@ struct hgb_conv {
     bool have_kernel = false;
     int variant = 0, chunk = 0, exchange = HGB_EXCHANGE_NCCL;
     bool overlap = true;   // boundary/interior split with the exchange under the interior kernel
+    bool fuse2 = true;     // 3x3: two iterations per pass where the schedule allows
     int cur = 0;
     bool uploaded = false;
     bool have_backup = false;
@@ -116,6 +117,21 @@ static int launch_stream(const hgb_conv *h, const CvShard &s, const double *in, 
     g.crows = crows;
     dim3 grid((h->W + kTW - 1) / kTW, (crows + chunk - 1) / chunk);
     kern<<<grid, Cfg::THREADS, Cfg::SMEM, st>>>(in, out, g, chunk, h->taps);
+    HGB_LAUNCHED();
+    return HGB_OK;
+}
+
+// rows [crow0, crow0+crows) advanced by TWO iterations in one pass (3x3 only)
+static int launch_fused2(const hgb_conv *h, const CvShard &s, const double *in, double *out, int crow0,
+                         int crows, cudaStream_t st) {
+    if (crows <= 0) return HGB_OK;
+    int chunk = h->chunk > 0 ? h->chunk : 64;   // measured on B200: profiles/r1c_conv3_fused_sweep.txt
+    if (chunk > crows) chunk = crows;
+    BandGeom g = geom(h, s);
+    g.crow0 = crow0;
+    g.crows = crows;
+    dim3 grid((h->W + kF2Out - 1) / kF2Out, (crows + chunk - 1) / chunk);
+    conv3_fused2_kernel<<<grid, kF2Threads, kF2Smem, st>>>(in, out, g, chunk, h->taps);
     HGB_LAUNCHED();
     return HGB_OK;
 }
@@ -287,9 +303,10 @@ int hgb_conv_set_kernel(hgb_conv *h, const double *kernel, int kw, int kh) {
 }
 
 int hgb_conv_tune(hgb_conv *h, int variant, int band_rows) {
-    HGB_ARG(h && variant >= 0 && variant <= 3 && band_rows >= 0, "handle / variant / band_rows");
+    HGB_ARG(h && variant >= 0 && variant <= 7 && band_rows >= 0, "handle / variant / band_rows");
     h->variant = variant & 1;
     h->overlap = !(variant & 2);
+    h->fuse2 = !(variant & 4);
     h->chunk = band_rows;
     return HGB_OK;
 }
@@ -376,7 +393,22 @@ int hgb_conv_step(hgb_conv *h, int iterations, float *ms) {
             HGB_CUDA(cudaSetDevice(s.dev->device));
             HGB_CUDA(cudaStreamWaitEvent(s.dev->stream2, s.dev->ev_begin, 0));
         }
-    for (int it = 0, cycle = 0; it < iterations; ++cycle) {
+    // One band, 3x3: two iterations per pass (conv3_fused2_kernel) while at least one plain iteration
+    // remains at the end, so that the state before the last iteration -- what the caller gets as
+    // `prev` -- exists in memory.
+    int fused = 0;
+    if (h->active == 1 && h->kw == 3 && h->kh == 3 && h->p == 1 && h->variant != 1 && h->fuse2) {
+        const int tail = (iterations & 1) ? 1 : 2;
+        for (; iterations - fused > tail; fused += 2) {
+            for (CvShard &s : h->sh) {
+                if (s.rows <= 0) continue;
+                HGB_CUDA(cudaSetDevice(s.dev->device));
+                HGB_TRY(launch_fused2(h, s, s.img[h->cur], s.img[h->cur ^ 1], s.row0, s.rows, s.dev->stream));
+            }
+            h->cur ^= 1;
+        }
+    }
+    for (int it = fused, cycle = 0; it < iterations; ++cycle) {
         const int d = min(depth, iterations - it);
         if (overlap && cycle > 0)
             for (CvShard &s : h->sh) {

@@ -283,3 +283,60 @@ def test_depth_can_change_between_steps_and_split_steps_agree(hgb, monkeypatch):
         cv.set_depth(1)
         cv.step(1)
         assert np.array_equal(cv.download(), want)
+
+
+# ---- 3x3 two-iterations-per-pass kernel (temporal blocking): bit-identical to separate passes ----
+FUSED = [(1, 1), (2, 1), (1, 2), (3, 3), (2, 7), (5, 2), (253, 4), (254, 3), (255, 5), (256, 6), (257, 9),
+         (508, 2), (509, 33), (511, 70), (1000, 37), (1271, 130)]
+
+
+@pytest.mark.parametrize("w,h", FUSED)
+@pytest.mark.parametrize("it,band", [(3, 0), (4, 0), (6, 1), (7, 2), (5, 3), (8, 5)])
+def test_fused_3x3_matches_oracle_on_edges_and_strip_seams(hgb, w, h, it, band):
+    """odd/even widths around the 254-column strip seam, tiny heights (top and bottom clamp in
+    the same chunk), arbitrary pad columns on input, odd/even iteration counts, chunk heights"""
+    from oracle import port
+    base = (synth.uniform01(w * 131 + h, h * (w + 2)) * 4 - 2).reshape(h, w + 2).copy()   # pads as given
+    kern = synth.kernel_dense(3, seed=w + it)
+    want_c, want_p = base.copy(), np.zeros_like(base)
+    port.conv_run(want_c, want_p, w, h, 1, kern, it)
+    with hgb.convolution.Conv2D(w, h, 1) as cv:
+        cv.set_kernel(kern).tune(0, band).upload(base)
+        cv.step(it)
+        got_c, got_p = cv.download(want_prev=True)
+    assert np.array_equal(got_c, want_c)
+    assert np.array_equal(got_p, want_p)          # state it-1 exists: the last iteration is a plain pass
+
+
+def test_fused_3x3_equals_unfused_at_size(hgb):
+    w, h, it = 4100, 2100, 9
+    img = synth.image_float(w, h, seed=5)
+    outs = []
+    for variant in (0, 4):                         # bit 2: no fusion
+        with hgb.convolution.Conv2D(w, h, 1) as cv:
+            cv.set_kernel(synth.kernel_dense(3)).tune(variant, 0).upload_dense(img)
+            cv.step(it)
+            outs.append(cv.download(want_prev=True))
+    assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
+
+
+def test_fused_3x3_split_steps_and_special_values(hgb):
+    """step(a) then step(b) == step(a+b); signed zeros / denormals / huge values pass through both stages"""
+    w, h = 300, 40
+    img = synth.image_float(w, h, seed=9) - 0.5
+    img[0, 0], img[3, 7], img[h - 1, w - 1], img[5, 5], img[9, 250:260] = -0.0, 5e-324, 1e300, -1e-310, 0.0
+    kern = synth.kernel_dense(3)
+    with hgb.convolution.Conv2D(w, h, 1) as cv:
+        cv.set_kernel(kern).upload_dense(img)
+        cv.step(11)
+        want = cv.download(want_prev=True)
+        cv.upload_dense(img)
+        cv.step(4)
+        cv.step(1)
+        cv.step(6)
+        got = cv.download(want_prev=True)
+        cv.tune(4, 0).upload_dense(img)
+        cv.step(11)
+        plain = cv.download(want_prev=True)
+    for a, b, c in zip(want, got, plain):
+        assert a.tobytes() == b.tobytes() == c.tobytes()

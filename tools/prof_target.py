@@ -22,5 +22,5 @@ else:
         p = k // 2
         with H.convolution.Conv2D(n, n, p) as cv:
             cv.set_kernel(synth.kernel_dense(k)).upload(synth.add_padding(dense, p))
-            print("k", k, "ms", cv.step(2), cv.step(2))
+            print("k", k, "ms", cv.step(5))     # 3x3: two fused passes (2 iterations each) + one plain pass
 H.lib().hgb_finalize()
