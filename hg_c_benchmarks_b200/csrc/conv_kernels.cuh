@@ -212,14 +212,18 @@ conv_stream_kernel(const double *__restrict__ in, double *__restrict__ out, Band
 //     row from intermediate row 0 as well, and output row H-1 its last one from row H-1.
 constexpr int kF2TW = 256;              // intermediate columns per CTA
 constexpr int kF2Out = kF2TW - 2;       // output columns per CTA
-constexpr int kF2Pitch = kF2TW + 4;     // shared-memory row pitch (doubles): 16-byte multiple, room for +2/+3 reads
+constexpr int kF2Pitch = kF2TW + 4;     // shared-memory row pitch (doubles): 16-byte multiple, room for the reads past TW
 constexpr int kF2Ring = 6;              // input rows in flight: two halves of three (the loop is unrolled by 3)
-constexpr int kF2Threads = kF2TW / 2;
 constexpr size_t kF2Smem = (size_t)(kF2Ring + 2) * kF2Pitch * sizeof(double) + kF2Ring * sizeof(uint64_t);
 
-__global__ void __launch_bounds__(kF2Threads)
+// C = columns per thread (2 or 4); kF2TW / C threads per CTA.  Measured equal on B200 (a pass moves
+// 4.39 GB, so its HBM floor is ~650 us; both variants take ~800 us for two iterations with the FP64
+// pipe ~69 % busy, ncu: profiles/r1c_conv3_fused_ncu_summary.txt); C = 2 is the default.
+template <int C>
+__global__ void __launch_bounds__(kF2TW / C)
 conv3_fused2_kernel(const double *__restrict__ in, double *__restrict__ out, BandGeom g, int chunk,
                     const __grid_constant__ Taps taps) {
+    constexpr int T = kF2TW / C, NV = C + 2;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     double *inring = reinterpret_cast<double *>(smem_raw);
     double *mid = inring + kF2Ring * kF2Pitch;
@@ -249,52 +253,66 @@ conv3_fused2_kernel(const double *__restrict__ in, double *__restrict__ out, Ban
     if (tid == 0)
         for (int i = 0; i < kF2Ring && i < nin; ++i) issue(i, i);
 
-    const int a = xs + 2 * tid;            // global column of this thread's first intermediate value
-    const int c0 = a + 1;                  // first of its two output columns
-    const bool has_out = tid < kF2Threads - 1 && c0 < g.W;
-    const bool st_pair = has_out && c0 + 1 < g.W;                // double2 store, else one column
-    const bool pad_left = has_out && c0 == 0;                    // update_borders of the output
-    const int pad_right = !has_out ? -1 : c0 == g.W - 1 ? 0 : c0 + 1 == g.W - 1 ? 1 : -1;
+    const int a = xs + C * tid;            // global column of this thread's first intermediate value
+    const int c0 = a + 1;                  // first of its C output columns
+    // output columns of the strip end at xs + TW - 2 (the last thread owns fewer) and at W - 1
+    const int nvalid = max(0, min(C, min(g.W, xs + kF2TW - 1) - c0));
+    const bool pad_left = nvalid > 0 && c0 == 0;                 // update_borders of the output
+    const int pad_right = g.W - 1 - c0;                          // this thread's output that is column W-1, if in [0, nvalid)
     const bool edge_strip = blockIdx.x == 0 || xs + kF2TW + 2 > g.W;
-    const int last = g.W - 1 - a;          // position of column W-1 among this thread's 4 intermediate values
+    const int last = g.W - 1 - a;          // position of column W-1 among this thread's intermediate values
     // chunks that hold image row 0 or H-1 take the variant of stage 2 with the row-alias rules
     const bool edge_rows = y0 == 0 || y0 + nrows >= g.H;
     double *const out_col = out + band_row_off(g, y0) + kLead + c0;
 
-    double a1[3][2], a2[3][2];
+    double a1[3][C], a2[3][C];
 #pragma unroll
-    for (int q = 0; q < 3; ++q) { a1[q][0] = a1[q][1] = 0.0; a2[q][0] = a2[q][1] = 0.0; }
+    for (int q = 0; q < 3; ++q)
+#pragma unroll
+        for (int c = 0; c < C; ++c) { a1[q][c] = 0.0; a2[q][c] = 0.0; }
 
-    auto store_row = [&](int o, double v0, double v1) {
+    auto store_row = [&](int o, const double (&val)[C]) {
         double *orow = out_col + (size_t)o * g.dp;
-        if (st_pair) *reinterpret_cast<double2 *>(orow) = make_double2(v0, v1);
-        else orow[0] = v0;
-        if (pad_left) orow[-1] = v0;
-        if (pad_right == 0) orow[1] = v0;
-        if (pad_right == 1) orow[2] = v1;
+#pragma unroll
+        for (int c = 0; c < C; c += 2) {
+            if (c + 1 < nvalid) *reinterpret_cast<double2 *>(orow + c) = make_double2(val[c], val[c + 1]);
+            else if (c < nvalid) orow[c] = val[c];
+        }
+        if (pad_left) orow[-1] = val[0];
+        if (pad_right >= 0 && pad_right < nvalid) {
+            double v = val[0];
+#pragma unroll
+            for (int c = 1; c < C; ++c) v = pad_right == c ? val[c] : v;
+            orow[pad_right + 1] = v;
+        }
+    };
+    auto load_row = [&](const double *row, double (&v)[NV]) {    // NV consecutive doubles, 16-byte aligned
+#pragma unroll
+        for (int q = 0; q < NV; q += 2) {
+            const double2 t = *reinterpret_cast<const double2 *>(row + q);
+            v[q] = t.x; v[q + 1] = t.y;
+        }
     };
 
     for (int k = 0, i0 = 0; i0 < nin; ++k, i0 += 3) {
         const int half = k & 1;                                  // ring slot of phase ph is 3*half + ph
         const uint32_t parity = (uint32_t)(k >> 1) & 1u;
-        const double *in_half = inring + half * 3 * kF2Pitch + 2 * tid;
-        double *mid_a = mid + half * kF2Pitch + 2 * tid;         // intermediate row j lives in slot j & 1 == (k + ph) & 1
-        double *mid_b = mid + (half ^ 1) * kF2Pitch + 2 * tid;
+        const double *in_half = inring + half * 3 * kF2Pitch + C * tid;
+        double *mid_a = mid + half * kF2Pitch + C * tid;         // intermediate row j lives in slot j & 1 == (k + ph) & 1
+        double *mid_b = mid + (half ^ 1) * kF2Pitch + C * tid;
 #pragma unroll
         for (int ph = 0; ph < 3; ++ph) {
             const int i = i0 + ph;
             if (i >= nin) break;
             mbar_wait(&full[3 * half + ph], parity);
             {   // stage 1: input row i feeds the intermediate rows it is the top / middle / bottom row of
-                const double *srow = in_half + ph * kF2Pitch;
-                const double2 p0 = *reinterpret_cast<const double2 *>(srow);
-                const double2 p1 = *reinterpret_cast<const double2 *>(srow + 2);
-                const double v[4] = {p0.x, p0.y, p1.x, p1.y};    // input columns a-1 .. a+2
+                double v[NV];                                    // input columns a-1 .. a+C
+                load_row(in_half + ph * kF2Pitch, v);
 #pragma unroll
                 for (int ky = 0; ky < 3; ++ky) {
                     const int sl = (ph - ky + 3) % 3;
 #pragma unroll
-                    for (int c = 0; c < 2; ++c) {
+                    for (int c = 0; c < C; ++c) {
                         double val = (ky == 0) ? 0.0 : a1[sl][c];
 #pragma unroll
                         for (int kx = 0; kx < 3; ++kx) val = __dadd_rn(val, __dmul_rn(taps.k[ky * 3 + kx], v[c + kx]));
@@ -305,21 +323,25 @@ conv3_fused2_kernel(const double *__restrict__ in, double *__restrict__ out, Ban
             // intermediate row j = i-2 (global row y0-1+j) is complete in accumulator slot (ph+1)%3
             const int j = i - 2;
             double *mrow = (ph == 1) ? mid_b : mid_a;
-            if (j >= 0) *reinterpret_cast<double2 *>(mrow) = make_double2(a1[(ph + 1) % 3][0], a1[(ph + 1) % 3][1]);
+            if (j >= 0) {
+#pragma unroll
+                for (int c = 0; c < C; c += 2)
+                    *reinterpret_cast<double2 *>(mrow + c) = make_double2(a1[(ph + 1) % 3][c], a1[(ph + 1) % 3][c + 1]);
+            }
             __syncthreads();               // intermediate row visible; input slot drained by everyone
             if (tid == 0 && i + kF2Ring < nin) issue(i + kF2Ring, 3 * half + ph);
             if (j < 0) continue;
             // stage 2: intermediate row j feeds output rows j, j-1, j-2 (relative to y0)
-            const double2 q0 = *reinterpret_cast<const double2 *>(mrow);
-            const double2 q1 = *reinterpret_cast<const double2 *>(mrow + 2);
-            double w[4] = {q0.x, q0.y, q1.x, q1.y};              // intermediate columns a .. a+3
+            double w[NV];                                        // intermediate columns a .. a+C+1
+            load_row(mrow, w);
             if (edge_strip) {              // update_borders of the intermediate state
                 if (a < 0) w[0] = w[1];
-                if (last >= 0 && last < 3) {
-                    const double wl = last == 0 ? w[0] : last == 1 ? w[1] : w[2];
-                    if (last < 1) w[1] = wl;
-                    if (last < 2) w[2] = wl;
-                    w[3] = wl;
+                if (last >= 0 && last < NV - 1) {
+                    double wl = w[0];
+#pragma unroll
+                    for (int q = 1; q < NV - 1; ++q) wl = last == q ? w[q] : wl;
+#pragma unroll
+                    for (int q = 1; q < NV; ++q) w[q] = q > last ? wl : w[q];
                 }
             }
             auto stage2 = [&](auto edge_tag) {
@@ -331,7 +353,7 @@ conv3_fused2_kernel(const double *__restrict__ in, double *__restrict__ out, Ban
                     const bool top = EDGE && ky == 1 && y0 + o == 0;            // warp-uniform
                     const bool bottom = EDGE && ky == 1 && y0 + o == g.H - 1;
 #pragma unroll
-                    for (int c = 0; c < 2; ++c) {
+                    for (int c = 0; c < C; ++c) {
                         double val = (ky == 0) ? 0.0 : a2[sl][c];
                         if (EDGE && top) { // intermediate row -1 aliases row 0: tap row 0 comes from this row too
                             val = 0.0;
@@ -348,9 +370,9 @@ conv3_fused2_kernel(const double *__restrict__ in, double *__restrict__ out, Ban
                     }
                     if (EDGE) {
                         const bool done = (ky == 2 && y0 + o != g.H - 1) || bottom;
-                        if (done && o >= 0 && o < nrows && has_out) store_row(o, a2[sl][0], a2[sl][1]);
+                        if (done && o >= 0 && o < nrows) store_row(o, a2[sl]);
                     } else {
-                        if (ky == 2 && o >= 0 && has_out) store_row(o, a2[sl][0], a2[sl][1]);   // o < nrows: i < nin
+                        if (ky == 2 && o >= 0) store_row(o, a2[sl]);   // o < nrows holds: i < nin
                     }
                 }
             };

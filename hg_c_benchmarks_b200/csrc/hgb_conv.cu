@@ -33,6 +33,7 @@ struct hgb_conv {
     int variant = 0, chunk = 0, exchange = HGB_EXCHANGE_NCCL;
     bool overlap = true;   // boundary/interior split with the exchange under the interior kernel
     bool fuse2 = true;     // 3x3: two iterations per pass where the schedule allows
+    int fuse_cols = 2;     // columns per thread of that kernel (2 or 4; measured equal, 2 slightly ahead)
     int cur = 0;
     bool uploaded = false;
     bool have_backup = false;
@@ -131,7 +132,8 @@ static int launch_fused2(const hgb_conv *h, const CvShard &s, const double *in, 
     g.crow0 = crow0;
     g.crows = crows;
     dim3 grid((h->W + kF2Out - 1) / kF2Out, (crows + chunk - 1) / chunk);
-    conv3_fused2_kernel<<<grid, kF2Threads, kF2Smem, st>>>(in, out, g, chunk, h->taps);
+    if (h->fuse_cols == 2) conv3_fused2_kernel<2><<<grid, kF2TW / 2, kF2Smem, st>>>(in, out, g, chunk, h->taps);
+    else conv3_fused2_kernel<4><<<grid, kF2TW / 4, kF2Smem, st>>>(in, out, g, chunk, h->taps);
     HGB_LAUNCHED();
     return HGB_OK;
 }
@@ -303,7 +305,8 @@ int hgb_conv_set_kernel(hgb_conv *h, const double *kernel, int kw, int kh) {
 }
 
 int hgb_conv_tune(hgb_conv *h, int variant, int band_rows) {
-    HGB_ARG(h && variant >= 0 && variant <= 7 && band_rows >= 0, "handle / variant / band_rows");
+    HGB_ARG(h && variant >= 0 && variant <= 15 && band_rows >= 0, "handle / variant / band_rows");
+    h->fuse_cols = (variant & 8) ? 4 : 2;
     h->variant = variant & 1;
     h->overlap = !(variant & 2);
     h->fuse2 = !(variant & 4);

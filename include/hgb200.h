@@ -142,7 +142,8 @@ int hgb_conv_create(hgb_conv **out, int inner_w, int inner_h, int padding, int n
 int hgb_conv_create_rank(hgb_conv **out, int inner_w, int inner_h, int padding);
 int hgb_conv_set_kernel(hgb_conv *h, const double *kernel, int kw, int kh);
 /* variant bit 0: generic kernel instead of the specialised one; bit 1: no boundary/interior overlap
- * in the multi-GPU step; bit 2: no two-iterations-per-pass kernel for 3x3; band_rows: output rows
+ * in the multi-GPU step; bit 2: no two-iterations-per-pass kernel for 3x3; bit 3: that kernel with 4 columns per thread instead
+ * of 2; band_rows: output rows
  * per CTA (0 = per-kernel default) */
 int hgb_conv_tune(hgb_conv *h, int variant, int band_rows);
 /* iterations per halo exchange (communication-avoiding deep halo, multi-GPU only): depth*p rows
