@@ -66,7 +66,8 @@ constexpr int kBnd = 32;   // boundary rows per side computed ahead of the excha
 static int eff_depth(const hgb_conv *h) {
     if (h->active <= 1 || h->p <= 0) return 1;
     int minrows = h->H / h->active;
-    int d = h->depth_req > 0 ? h->depth_req : 8;
+    // automatic: 8; 16 for 3x3, whose non-final iterations of a cycle run two per pass
+    int d = h->depth_req > 0 ? h->depth_req : (h->p == 1 && h->fuse2 ? 16 : 8);
     if (d > h->halo / h->p) d = h->halo / h->p;
     if (d > minrows / h->p) d = minrows / h->p;
     return d < 1 ? 1 : d;
@@ -400,7 +401,8 @@ int hgb_conv_step(hgb_conv *h, int iterations, float *ms) {
     // remains at the end, so that the state before the last iteration -- what the caller gets as
     // `prev` -- exists in memory.
     int fused = 0;
-    if (h->active == 1 && h->kw == 3 && h->kh == 3 && h->p == 1 && h->variant != 1 && h->fuse2) {
+    const bool fuse_ok = h->kw == 3 && h->kh == 3 && h->p == 1 && h->variant != 1 && h->fuse2;
+    if (h->active == 1 && fuse_ok) {
         const int tail = (iterations & 1) ? 1 : 2;
         for (; iterations - fused > tail; fused += 2) {
             for (CvShard &s : h->sh) {
@@ -421,14 +423,22 @@ int hgb_conv_step(hgb_conv *h, int iterations, float *ms) {
             }
         for (int t = 0; t < d; ++t, ++it) {
             const int cur = h->cur, nxt = cur ^ 1;
-            const bool last = t == d - 1;
-            const int ext = (d - 1 - t) * h->p;        // fringe rows beyond the band (0 on the last)
+            // 3x3: iterations t and t+1 as ONE pass (conv3_fused2_kernel) unless t+1 is the final
+            // iteration of the whole step (the state before it must exist in memory: it is `prev`)
+            const bool pair = fuse_ok && t + 1 < d && it + 2 < iterations;
+            const int steps = pair ? 2 : 1;
+            const bool last = t + steps == d;            // this launch ends the cycle: exchange follows
+            const int ext = (d - t - steps) * h->p;      // fringe rows beyond the band (0 when last)
+            auto run = [&](const CvShard &s, int row0, int nrows, cudaStream_t st) {
+                return pair ? launch_fused2(h, s, s.img[cur], s.img[nxt], row0, nrows, st)
+                            : launch_conv(h, s, s.img[cur], s.img[nxt], row0, nrows, st);
+            };
             if (!last || !overlap) {
                 for (CvShard &s : h->sh) {
                     if (s.rows <= 0) continue;
                     HGB_CUDA(cudaSetDevice(s.dev->device));
                     const int lo = max(0, s.row0 - ext), hi = min(h->H, s.row0 + s.rows + ext);
-                    HGB_TRY(launch_conv(h, s, s.img[cur], s.img[nxt], lo, hi - lo, s.dev->stream));
+                    HGB_TRY(run(s, lo, hi - lo, s.dev->stream));
                 }
                 if (last) HGB_TRY(halo_exchange(h, nxt));
             } else {
@@ -438,19 +448,20 @@ int hgb_conv_step(hgb_conv *h, int iterations, float *ms) {
                     cudaStream_t sb = s.dev->stream2;
                     HGB_CUDA(cudaEventRecord(s.dev->ev_int[0], s.dev->stream));      // ev_pre
                     HGB_CUDA(cudaStreamWaitEvent(sb, s.dev->ev_int[0], 0));
-                    HGB_TRY(launch_conv(h, s, s.img[cur], s.img[nxt], s.row0, kBnd, sb));
-                    HGB_TRY(launch_conv(h, s, s.img[cur], s.img[nxt], s.row0 + s.rows - kBnd, kBnd, sb));
+                    HGB_TRY(run(s, s.row0, kBnd, sb));
+                    HGB_TRY(run(s, s.row0 + s.rows - kBnd, kBnd, sb));
                 }
                 HGB_TRY(halo_exchange(h, nxt, true));
                 for (CvShard &s : h->sh) {
                     if (s.rows <= 0) continue;
                     HGB_CUDA(cudaSetDevice(s.dev->device));
                     HGB_CUDA(cudaEventRecord(s.dev->ev_bnd[0], s.dev->stream2));     // ev_x
-                    HGB_TRY(launch_conv(h, s, s.img[cur], s.img[nxt], s.row0 + kBnd, s.rows - 2 * kBnd,
-                                        s.dev->stream));
+                    HGB_TRY(run(s, s.row0 + kBnd, s.rows - 2 * kBnd, s.dev->stream));
                 }
             }
             h->cur = nxt;
+            t += steps - 1;
+            it += steps - 1;                             // the loop header adds the other one
         }
     }
     if (overlap)

@@ -147,8 +147,8 @@ int hgb_conv_set_kernel(hgb_conv *h, const double *kernel, int kw, int kh);
  * per CTA (0 = per-kernel default) */
 int hgb_conv_tune(hgb_conv *h, int variant, int band_rows);
 /* iterations per halo exchange (communication-avoiding deep halo, multi-GPU only): depth*p rows
- * travel once per `depth` iterations, the fringe is recomputed in between; 0 = automatic (8, capped
- * by 32/p and the band height).  Returns the depth in effect (>= 1) or a negative error. */
+ * travel once per `depth` iterations, the fringe is recomputed in between; 0 = automatic (8, or 16 for
+ * padding 1 where the non-final iterations of a cycle run two per pass; capped by 32/p and the band height).  Returns the depth in effect (>= 1) or a negative error. */
 int hgb_conv_set_depth(hgb_conv *h, int depth);
 int hgb_conv_set_exchange(hgb_conv *h, int kind);           /* HGB_EXCHANGE_NCCL (send/recv) or _P2P (peer copies) */
 /* rank mode: each rank passes ONLY its own band: rows [row0, row0+rows) of the image */

@@ -24,7 +24,7 @@ for rows_total in heights:
         p = k // 2
         modes = [("nccl", H.EXCHANGE_NCCL), ("p2p", H.EXCHANGE_P2P)] if sp else [("nccl", H.EXCHANGE_NCCL)]
         for ename, exch in modes:
-            for depth in (1, 2, 4, 8, 16):
+            for depth in (1, 2, 4, 8, 16, 32):
                 cv = H.convolution.Conv2D(W, rows_total, p, ngpus=world if sp else None)
                 if sp:
                     cv.set_exchange(exch)
