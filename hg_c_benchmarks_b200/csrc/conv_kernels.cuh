@@ -382,8 +382,6 @@ conv3_fused2_kernel(const double *__restrict__ in, double *__restrict__ out, Ban
     }
 }
 
-// sequential row-major checksum (reference get_checksum, convolution-util.c:63-71): see
-// conv_checksum_seq_kernel below.
 // add_padding's pad columns (reference src/convolution/convolution-util.c:258-269 via
 // init_padded_image/update_borders): for stored rows [r0, r1) of the band (halo rows included)
 // copy inner pixel 0 into the p columns left of it and pixel W-1 into the p columns right of it.
@@ -397,6 +395,7 @@ conv_pad_columns_kernel(double *__restrict__ img, BandGeom g, int r0, int r1) {
     for (int q = i; q < g.p; q += 8) { row[-1 - q] = left; row[g.W + q] = right; }
 }
 
+// sequential row-major checksum (reference get_checksum, convolution-util.c:63-71):
 // one warp stages 32 doubles at a time, lane 0 adds them in order.  Exact but
 // serial; used by tests and the CLI path only.
 __global__ void __launch_bounds__(32)

@@ -65,6 +65,7 @@ static int launch_step(const hgb_nbody *h, const NbShard &s, const double *src, 
     }
 #define HGB_VW(B, U) HGB_V(B, U, 24) HGB_V(B, U, 32) HGB_V(B, U, 40)
     HGB_VW(128, 1) HGB_VW(128, 2) HGB_VW(128, 4)
+    HGB_V(128, 1, 28) HGB_V(128, 2, 28) HGB_V(128, 4, 28)   // 7 CTAs per SM: 1036 slots
     HGB_VW(256, 1) HGB_VW(256, 2) HGB_VW(256, 4)
 #undef HGB_VW
 #undef HGB_V
@@ -191,7 +192,8 @@ int hgb_nbody_tune(hgb_nbody *h, int block, int unroll, int warps) {
     HGB_ARG(h, "handle");
     HGB_ARG(block == 0 || block == 128 || block == 256, "block in {128,256}");
     HGB_ARG(unroll == 0 || unroll == 1 || unroll == 2 || unroll == 4, "unroll in {1,2,4}");
-    HGB_ARG(warps == 0 || warps == 24 || warps == 32 || warps == 40, "warps in {24,32,40}");
+    HGB_ARG(warps == 0 || warps == 24 || warps == 28 || warps == 32 || warps == 40, "warps in {24,28,32,40}");
+    HGB_ARG(warps != 28 || block != 256, "warps = 28 needs 128-thread CTAs");
     h->block = block;
     h->unroll = unroll;
     h->warps = warps;

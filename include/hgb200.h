@@ -84,7 +84,7 @@ int hgb_nbody_create(hgb_nbody **out, int n, int ngpus);
 int hgb_nbody_create_rank(hgb_nbody **out, int n);
 int hgb_nbody_config(hgb_nbody *h, int mode, int exchange);
 /* kernel variant; 0 = default: threads per CTA {128,256}, sources per unrolled group/2 {1,2,4},
- * resident warps per SM the register allocation allows {24,32,40} */
+ * resident warps per SM the register allocation allows {24,28,32,40} (28: 128-thread CTAs only) */
 int hgb_nbody_tune(hgb_nbody *h, int block, int unroll, int warps);
 int hgb_nbody_upload(hgb_nbody *h, const double *pos_aos);       /* all n bodies */
 /* `iterations` steps; *ms (may be NULL) = device time, CUDA events, max over local devices */
