@@ -211,6 +211,33 @@ def test_full_size_16k_bands_vs_oracle(hgb, k):
         assert np.array_equal(got[r0:r0 + 256], want), (k, r0)
 
 
+@pytest.mark.parametrize("it", [3, 6])
+def test_full_size_16k_fused_passes_vs_oracle(hgb, it):
+    """16384 x 16384 float image, 3x3, `it` iterations (two per pass + the plain final ones): bands
+    recomputed by the oracle with an `it`-row margin (pollution from the sub-image's artificial
+    edges travels one row per iteration), incl. the true top and bottom edges; and the whole image
+    against the one-iteration-per-pass kernel."""
+    from oracle import port
+    n, p = 16384, 1
+    kern = synth.kernel_dense(3)
+    dense = synth.image_float(n, n, seed=3)
+    with hgb.convolution.Conv2D(n, n, p) as cv:
+        cv.set_kernel(kern).upload_dense(dense)
+        cv.step(it)
+        got = cv.download()
+        cv.tune(4, 0).upload_dense(dense)                      # bit 2: plain passes only
+        cv.step(it)
+        plain = cv.download()
+    assert np.array_equal(got, plain)
+    del plain
+    for r0 in (0, 7777, n - 256):
+        lo, hi = max(0, r0 - it), min(n, r0 + 256 + it)
+        a = synth.add_padding(dense[lo:hi], p)
+        b = np.zeros_like(a)
+        port.conv_run(a, b, n, hi - lo, p, kern, it)
+        assert np.array_equal(got[r0:r0 + 256], a[r0 - lo:r0 - lo + 256]), r0
+
+
 def _oracle_rows(port, inp, w, h, p, kern, r0, r1):
     """oracle output rows [r0, r1) without allocating a second full image: run it on the
     sub-image [r0-p, r1+p) whose first/last rows are only touched through clamping when they
