@@ -382,6 +382,156 @@ conv3_fused2_kernel(const double *__restrict__ in, double *__restrict__ out, Ban
     }
 }
 
+// ---- 3x3, two iterations per pass, warp-independent variant ------------------------------
+// Same arithmetic and the same row/column alias rules as conv3_fused2_kernel, but the intermediate
+// state never touches shared memory: a WARP owns 64 intermediate columns (2 per lane) and outputs
+// the 62 inside them; the two intermediate values a lane needs from its right neighbour come by
+// warp shuffle, so there is no CTA-wide barrier per row.  The input ring is still shared by the
+// CTA's warps: `full` mbarriers announce a landed row, `empty` mbarriers (one arrival per warp)
+// hand a slot back to the producer lane, which refills it five rows ahead.
+constexpr int kF2wWarps = 4;
+constexpr int kF2wOut = 62 * kF2wWarps;      // output columns per CTA (248)
+constexpr int kF2wRow = 256;                 // staged doubles per input row: columns xs-1 .. xs+254
+constexpr size_t kF2wSmem = (size_t)kF2Ring * kF2wRow * sizeof(double) + 2 * kF2Ring * sizeof(uint64_t);
+
+__global__ void __launch_bounds__(kF2wWarps * 32)
+conv3_fused2w_kernel(const double *__restrict__ in, double *__restrict__ out, BandGeom g, int chunk,
+                     const __grid_constant__ Taps taps) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    double *inring = reinterpret_cast<double *>(smem_raw);
+    uint64_t *full = reinterpret_cast<uint64_t *>(inring + kF2Ring * kF2wRow);
+    uint64_t *empty = full + kF2Ring;
+
+    const int xs = blockIdx.x * kF2wOut - 1;                     // first intermediate column of the CTA
+    const int y0 = g.crow0 + blockIdx.y * chunk;                 // first output row (global)
+    const int nrows = min(chunk, g.crow0 + g.crows - y0);
+    const int nin = nrows + 4;                                   // input rows y0-2 .. y0+nrows+1
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < kF2Ring; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], kF2wWarps); }
+        mbar_init_fence();
+    }
+    __syncthreads();
+
+    const double *in_strip = in + kLead + (xs - 1);              // even column: 16-byte aligned
+    auto issue = [&](int i, int slot) {                          // producer lane: input row i into `slot`
+        const int gr = min(max(y0 - 2 + i, 0), g.H - 1);         // aliased pad rows == clamp
+        mbar_expect_tx(&full[slot], (uint32_t)(kF2wRow * sizeof(double)));
+        bulk_g2s(inring + slot * kF2wRow, in_strip + band_row_off(g, gr), kF2wRow * sizeof(double), &full[slot]);
+    };
+    if (tid == 0)
+        for (int i = 0; i < kF2Ring && i < nin; ++i) issue(i, i);
+
+    const int a = xs + 62 * warp + 2 * lane;   // global column of this lane's first intermediate value
+    const int c0 = a + 1;                      // first of its two output columns
+    const int nvalid = lane == 31 ? 0 : max(0, min(2, g.W - c0));
+    const bool pad_left = nvalid > 0 && c0 == 0;
+    const int pad_right = g.W - 1 - c0;        // which of the two outputs is column W-1 (if 0 or 1)
+    const bool edge_strip = blockIdx.x == 0 || xs + kF2wRow > g.W;
+    const int last = g.W - 1 - a;
+    const bool edge_rows = y0 == 0 || y0 + nrows >= g.H;
+    double *const out_col = out + band_row_off(g, y0) + kLead + c0;
+
+    double a1[3][2], a2[3][2];
+#pragma unroll
+    for (int q = 0; q < 3; ++q) { a1[q][0] = a1[q][1] = 0.0; a2[q][0] = a2[q][1] = 0.0; }
+
+    auto store_row = [&](int o, double v0, double v1) {
+        double *orow = out_col + (size_t)o * g.dp;
+        if (nvalid == 2) *reinterpret_cast<double2 *>(orow) = make_double2(v0, v1);
+        else if (nvalid == 1) orow[0] = v0;
+        if (pad_left) orow[-1] = v0;
+        if (pad_right >= 0 && pad_right < nvalid) orow[pad_right + 1] = pad_right == 0 ? v0 : v1;
+    };
+    for (int k = 0, i0 = 0; i0 < nin; ++k, i0 += 3) {
+        const int half = k & 1;                                  // ring slot of phase ph is 3*half + ph
+        const uint32_t parity = (uint32_t)(k >> 1) & 1u;
+        const double *in_half = inring + half * 3 * kF2wRow + 62 * warp + 2 * lane;
+#pragma unroll
+        for (int ph = 0; ph < 3; ++ph) {
+            const int i = i0 + ph;
+            if (i >= nin) break;
+            const int slot = 3 * half + ph;
+            mbar_wait(&full[slot], parity);
+            const double *srow = in_half + ph * kF2wRow;
+            const double2 p0 = *reinterpret_cast<const double2 *>(srow);
+            const double2 p1 = *reinterpret_cast<const double2 *>(srow + 2);
+            const double v[4] = {p0.x, p0.y, p1.x, p1.y};        // input columns a-1 .. a+2
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[slot]);            // this warp has the row in registers
+            if (tid == 0 && i >= 1 && i + kF2Ring - 1 < nin) {
+                // row i+5 goes where row i-1 was, once every warp has handed that slot back
+                const int pslot = ph == 0 ? 3 * (half ^ 1) + 2 : slot - 1;
+                mbar_wait(&empty[pslot], (uint32_t)(((i - 1) / kF2Ring) & 1));
+                issue(i + kF2Ring - 1, pslot);
+            }
+#pragma unroll
+            for (int ky = 0; ky < 3; ++ky) {                     // stage 1
+                const int sl = (ph - ky + 3) % 3;
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    double val = (ky == 0) ? 0.0 : a1[sl][c];
+#pragma unroll
+                    for (int kx = 0; kx < 3; ++kx) val = __dadd_rn(val, __dmul_rn(taps.k[ky * 3 + kx], v[c + kx]));
+                    a1[sl][c] = val;
+                }
+            }
+            const int j = i - 2;           // intermediate row (global y0-1+j) complete in slot (ph+1)%3
+            if (j < 0) continue;
+            double w[4];                   // intermediate columns a .. a+3: own pair + the right neighbour's
+            w[0] = a1[(ph + 1) % 3][0];
+            w[1] = a1[(ph + 1) % 3][1];
+            w[2] = __shfl_down_sync(0xffffffffu, w[0], 1);
+            w[3] = __shfl_down_sync(0xffffffffu, w[1], 1);
+            if (edge_strip) {              // update_borders of the intermediate state
+                if (a < 0) w[0] = w[1];
+                if (last >= 0 && last < 3) {
+                    const double wl = last == 0 ? w[0] : last == 1 ? w[1] : w[2];
+                    if (last < 1) w[1] = wl;
+                    if (last < 2) w[2] = wl;
+                    w[3] = wl;
+                }
+            }
+            auto stage2 = [&](auto edge_tag) {
+                constexpr bool EDGE = decltype(edge_tag)::value;
+#pragma unroll
+                for (int ky = 0; ky < 3; ++ky) {
+                    const int sl = (ph + 1 - ky + 3) % 3;
+                    const int o = j - ky;                        // output row relative to y0
+                    const bool top = EDGE && ky == 1 && y0 + o == 0;
+                    const bool bottom = EDGE && ky == 1 && y0 + o == g.H - 1;
+#pragma unroll
+                    for (int c = 0; c < 2; ++c) {
+                        double val = (ky == 0) ? 0.0 : a2[sl][c];
+                        if (EDGE && top) {
+                            val = 0.0;
+#pragma unroll
+                            for (int kx = 0; kx < 3; ++kx) val = __dadd_rn(val, __dmul_rn(taps.k[kx], w[c + kx]));
+                        }
+#pragma unroll
+                        for (int kx = 0; kx < 3; ++kx) val = __dadd_rn(val, __dmul_rn(taps.k[ky * 3 + kx], w[c + kx]));
+                        if (EDGE && bottom) {
+#pragma unroll
+                            for (int kx = 0; kx < 3; ++kx) val = __dadd_rn(val, __dmul_rn(taps.k[6 + kx], w[c + kx]));
+                        }
+                        a2[sl][c] = val;
+                    }
+                    if (EDGE) {
+                        const bool done = (ky == 2 && y0 + o != g.H - 1) || bottom;
+                        if (done && o >= 0 && o < nrows) store_row(o, a2[sl][0], a2[sl][1]);
+                    } else {
+                        if (ky == 2 && o >= 0) store_row(o, a2[sl][0], a2[sl][1]);
+                    }
+                }
+            };
+            if (edge_rows) stage2(std::true_type{});
+            else stage2(std::false_type{});
+        }
+    }
+}
+
 // add_padding's pad columns (reference src/convolution/convolution-util.c:258-269 via
 // init_padded_image/update_borders): for stored rows [r0, r1) of the band (halo rows included)
 // copy inner pixel 0 into the p columns left of it and pixel W-1 into the p columns right of it.

@@ -33,6 +33,7 @@ struct hgb_conv {
     int variant = 0, chunk = 0, exchange = HGB_EXCHANGE_NCCL;
     bool overlap = true;   // boundary/interior split with the exchange under the interior kernel
     bool fuse2 = true;     // 3x3: two iterations per pass where the schedule allows
+    bool fuse_warp = false; // warp-independent variant of that kernel (shuffles instead of a shared-memory row)
     int fuse_cols = 2;     // columns per thread of that kernel (2 or 4; measured equal, 2 slightly ahead)
     int cur = 0;
     bool uploaded = false;
@@ -132,6 +133,12 @@ static int launch_fused2(const hgb_conv *h, const CvShard &s, const double *in, 
     BandGeom g = geom(h, s);
     g.crow0 = crow0;
     g.crows = crows;
+    if (h->fuse_warp) {
+        dim3 gridw((h->W + kF2wOut - 1) / kF2wOut, (crows + chunk - 1) / chunk);
+        conv3_fused2w_kernel<<<gridw, kF2wWarps * 32, kF2wSmem, st>>>(in, out, g, chunk, h->taps);
+        HGB_LAUNCHED();
+        return HGB_OK;
+    }
     dim3 grid((h->W + kF2Out - 1) / kF2Out, (crows + chunk - 1) / chunk);
     if (h->fuse_cols == 2) conv3_fused2_kernel<2><<<grid, kF2TW / 2, kF2Smem, st>>>(in, out, g, chunk, h->taps);
     else conv3_fused2_kernel<4><<<grid, kF2TW / 4, kF2Smem, st>>>(in, out, g, chunk, h->taps);
@@ -306,7 +313,8 @@ int hgb_conv_set_kernel(hgb_conv *h, const double *kernel, int kw, int kh) {
 }
 
 int hgb_conv_tune(hgb_conv *h, int variant, int band_rows) {
-    HGB_ARG(h && variant >= 0 && variant <= 15 && band_rows >= 0, "handle / variant / band_rows");
+    HGB_ARG(h && variant >= 0 && variant <= 31 && band_rows >= 0, "handle / variant / band_rows");
+    h->fuse_warp = (variant & 16) != 0;
     h->fuse_cols = (variant & 8) ? 4 : 2;
     h->variant = variant & 1;
     h->overlap = !(variant & 2);

@@ -318,7 +318,8 @@ FUSED = [(1, 1), (2, 1), (1, 2), (3, 3), (2, 7), (5, 2), (253, 4), (254, 3), (25
 
 
 @pytest.mark.parametrize("w,h", FUSED)
-@pytest.mark.parametrize("it,band,variant", [(3, 0, 0), (4, 0, 8), (6, 1, 0), (7, 2, 8), (5, 3, 0), (8, 5, 0), (5, 4, 8)])
+@pytest.mark.parametrize("it,band,variant", [(3, 0, 0), (4, 0, 8), (6, 1, 0), (7, 2, 8), (5, 3, 0), (8, 5, 0), (5, 4, 8),
+                                             (3, 0, 16), (6, 1, 16), (7, 2, 16), (8, 5, 16)])
 def test_fused_3x3_matches_oracle_on_edges_and_strip_seams(hgb, w, h, it, band, variant):
     """odd/even widths around the 254-column strip seam, tiny heights (top and bottom clamp in
     the same chunk), arbitrary pad columns on input, odd/even iteration counts, chunk heights"""
@@ -328,7 +329,7 @@ def test_fused_3x3_matches_oracle_on_edges_and_strip_seams(hgb, w, h, it, band, 
     want_c, want_p = base.copy(), np.zeros_like(base)
     port.conv_run(want_c, want_p, w, h, 1, kern, it)
     with hgb.convolution.Conv2D(w, h, 1) as cv:
-        cv.set_kernel(kern).tune(variant, band).upload(base)     # variant 0: 2 columns per thread, 8: 4
+        cv.set_kernel(kern).tune(variant, band).upload(base)     # variant 0: 2 columns per thread, 8: 4, 16: warp-independent
         cv.step(it)
         got_c, got_p = cv.download(want_prev=True)
     assert np.array_equal(got_c, want_c)
@@ -339,7 +340,7 @@ def test_fused_3x3_equals_unfused_at_size(hgb):
     w, h, it = 4100, 2100, 9
     img = synth.image_float(w, h, seed=5)
     outs = []
-    for variant in (0, 8, 4):                      # 2 / 4 columns per thread, bit 2: no fusion
+    for variant in (0, 8, 16, 4):                  # 2 / 4 columns per thread, warp-independent, bit 2: no fusion
         with hgb.convolution.Conv2D(w, h, 1) as cv:
             cv.set_kernel(synth.kernel_dense(3)).tune(variant, 0).upload_dense(img)
             cv.step(it)

@@ -11,7 +11,7 @@ img = synth.image_float(n, n, seed=3)
 with H.convolution.Conv2D(n, n, 1) as cv:
     cv.set_kernel(synth.kernel_dense(3)).upload_dense(img)
     ref = None
-    for variant, band in [(4, 0), (8, 32), (8, 64), (8, 128), (0, 16), (0, 32), (0, 48), (0, 64), (0, 96), (0, 128), (0, 256)]:
+    for variant, band in [(4, 0), (8, 64), (0, 32), (0, 64), (0, 128), (16, 16), (16, 32), (16, 48), (16, 64), (16, 96), (16, 128), (16, 256)]:
         cv.tune(variant, band).upload_dense(img)
         cv.step(5)
         chk = cv.checksum() if n <= 4096 else None
