@@ -3,6 +3,7 @@
 // drop-in for the reference's run() (src/nbody/nbody-run.c:27-37).
 #include "hgb_common.cuh"
 #include "nbody_kernels.cuh"
+#include "nbody_sym.cuh"
 
 using namespace hgb;
 
@@ -19,6 +20,7 @@ struct NbShard {
     double *mass = nullptr;      // integrator extension: npad masses, zero beyond n
     int *tlist = nullptr;
     int tlist_cap = 0;
+    int *sym_ctl = nullptr;      // pair-symmetric kernel: ticket, range flag, done[] (nbody_sym.cuh)
 };
 }  // namespace
 
@@ -30,6 +32,8 @@ struct hgb_nbody {
     int cur = 0;  // state[cur] holds the newest positions
     bool uploaded = false;
     bool dynamics = false;  // hgb_nbody_set_dynamics was called
+    int sym = 0;            // pair-symmetric kernel variant R*100 + U*10 + CTAs/SM (0 = off)
+    int sym_min_n = 0;      // ... used when n >= sym_min_n, one GPU, EXACT mode
     double dt = 0.0;
     std::vector<NbShard> sh;
 };
@@ -39,17 +43,20 @@ static int g_default_exchange = HGB_EXCHANGE_NCCL;
 
 template <int BLOCK, int UNROLL, int WARPS>
 static void launch_variant(bool fast, int grid, cudaStream_t st, const double *src, int npad, int n,
-                           int t0, int count, const int *tlist, const PeerOut &out, double *out_list) {
+                           int t0, int count, const int *tlist, const PeerOut &out, double *out_list,
+                           const int *run_if) {
+    const Dynamics none{nullptr, nullptr, 0.0};
     if (fast)
         nbody_step_kernel<BLOCK, UNROLL, WARPS, true><<<grid, BLOCK, 0, st>>>(src, npad, n, t0, count,
-                                                                            tlist, out, out_list);
+                                                                            tlist, out, out_list, none, run_if);
     else
         nbody_step_kernel<BLOCK, UNROLL, WARPS, false><<<grid, BLOCK, 0, st>>>(src, npad, n, t0, count,
-                                                                             tlist, out, out_list);
+                                                                             tlist, out, out_list, none, run_if);
 }
 
 static int launch_step(const hgb_nbody *h, const NbShard &s, const double *src, int t0, int count,
-                       const int *tlist, const PeerOut &out, double *out_list) {
+                       const int *tlist, const PeerOut &out, double *out_list,
+                       const int *run_if = nullptr) {
     if (count <= 0) return HGB_OK;
     const bool fast = h->mode == HGB_NBODY_FAST;
     const int block = h->block ? h->block : 128;
@@ -59,7 +66,7 @@ static int launch_step(const hgb_nbody *h, const NbShard &s, const double *src, 
     cudaStream_t st = s.dev->stream;
 #define HGB_V(B, U, W)                                                                             \
     if (block == B && unroll == U && warps == W) {                                                 \
-        launch_variant<B, U, W>(fast, grid, st, src, h->npad, h->n, t0, count, tlist, out, out_list); \
+        launch_variant<B, U, W>(fast, grid, st, src, h->npad, h->n, t0, count, tlist, out, out_list, run_if); \
         HGB_LAUNCHED();                                                                            \
         return HGB_OK;                                                                             \
     }
@@ -71,6 +78,62 @@ static int launch_step(const hgb_nbody *h, const NbShard &s, const double *src, 
 #undef HGB_V
     set_error("no nbody kernel variant block=%d unroll=%d warps=%d", block, unroll, warps);
     return HGB_ERR_ARG;
+}
+
+// ---- pair-symmetric step (nbody_sym.cuh): one GPU, EXACT mode, all n targets --------------
+static int g_default_sym = -1, g_default_sym_min_n = -1;   // -1: read HGB_NBODY_SYM / HGB_NBODY_SYM_MIN_N
+constexpr int kSymDefaultVariant = 224;                    // R = 2, U = 2, 4 CTAs (16 warps) per SM
+constexpr int kSymDefaultMinN = 262144;                    // below this the wavefront ramp dominates
+
+static bool sym_variant_known(int v) {
+    switch (v) {
+        case 124: case 146: case 148: case 216: case 224: case 225: case 226: case 234: case 413: case 423:
+            return true;
+    }
+    return false;
+}
+
+template <int R, int U, int CTAS>
+static int launch_sym_variant(cudaStream_t st, int sms, const double *src, int npad, int n, double *acc, int *ctl) {
+    const size_t smem = (size_t)kSymWarps * 6 * 3 * 32 * R * sizeof(double);
+    static bool attr_set = false;   // per instantiation
+    if (!attr_set) {
+        HGB_CUDA(cudaFuncSetAttribute(nbody_sym_kernel<R, U, CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)smem));
+        attr_set = true;
+    }
+    nbody_sym_kernel<R, U, CTAS><<<sms * CTAS, kSymWarps * 32, smem, st>>>(src, npad, n, acc, ctl);
+    HGB_LAUNCHED();
+    return HGB_OK;
+}
+
+static bool sym_applies(const hgb_nbody *h) {
+    return h->sym != 0 && h->world == 1 && h->mode == HGB_NBODY_EXACT && h->n >= h->sym_min_n;
+}
+
+// whole step on shard s: tickets/flags reset, wavefront kernel, G*acc, conditional redo
+static int launch_sym(const hgb_nbody *h, NbShard &s, const double *src, const PeerOut &out) {
+    cudaStream_t st = s.dev->stream;
+    const int R = h->sym / 100, tiles = (h->n + 32 * R - 1) / (32 * R);
+    if (!s.sym_ctl) HGB_CUDA(cudaMalloc(&s.sym_ctl, sizeof(int) * (kSymCtlInts + h->npad / 32 + 1)));
+    HGB_CUDA(cudaMemsetAsync(s.sym_ctl, 0, sizeof(int) * kSymCtlInts, st));
+    HGB_CUDA(cudaMemsetAsync(s.sym_ctl + kSymCtlInts, 0xFF, sizeof(int) * tiles, st));   // done[] = -1
+    int sms = 0;
+    HGB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s.dev->device));
+    double *acc = s.stage;   // the AoS staging buffer is idle between upload and download
+    int rc = HGB_ERR_ARG;
+    switch (h->sym) {
+#define HGB_SYM(R_, U_, C_) case R_ * 100 + U_ * 10 + C_: rc = launch_sym_variant<R_, U_, C_>(st, sms, src, h->npad, h->n, acc, s.sym_ctl); break;
+        HGB_SYM(1, 2, 4) HGB_SYM(1, 4, 6) HGB_SYM(1, 4, 8) HGB_SYM(2, 1, 6) HGB_SYM(2, 2, 4) HGB_SYM(2, 2, 5)
+        HGB_SYM(2, 2, 6) HGB_SYM(2, 3, 4) HGB_SYM(4, 1, 3) HGB_SYM(4, 2, 3)
+#undef HGB_SYM
+        default: set_error("no pair-symmetric nbody variant %d", h->sym);
+    }
+    HGB_TRY(rc);
+    nbody_sym_finish_kernel<<<(h->n + 255) / 256, 256, 0, st>>>(acc, h->npad, h->n, out);
+    HGB_LAUNCHED();
+    // never taken for sane input: an operand left the fast-path range -> ordinary kernel redoes the step
+    return launch_step(h, s, src, 0, h->n, nullptr, out, nullptr, s.sym_ctl + 1);
 }
 
 static int nb_alloc(hgb_nbody *h) {
@@ -87,7 +150,33 @@ static int nb_alloc(hgb_nbody *h) {
     return HGB_OK;
 }
 
+static void sym_defaults(hgb_nbody *h) {
+    if (g_default_sym < 0) {
+        const char *e = getenv("HGB_NBODY_SYM");
+        int v = e ? atoi(e) : 0;
+        if (v == 1) v = kSymDefaultVariant;
+        g_default_sym = sym_variant_known(v) ? v : 0;
+    }
+    if (g_default_sym_min_n < 0) {
+        const char *e = getenv("HGB_NBODY_SYM_MIN_N");
+        g_default_sym_min_n = e ? atoi(e) : kSymDefaultMinN;
+        if (g_default_sym_min_n < 0) g_default_sym_min_n = 0;
+    }
+    h->sym = g_default_sym;
+    h->sym_min_n = g_default_sym_min_n;
+}
+
 extern "C" {
+
+int hgb_nbody_set_symmetric(hgb_nbody *h, int variant, int min_n) {
+    HGB_ARG(h, "handle");
+    if (variant == 1) variant = kSymDefaultVariant;
+    HGB_ARG(variant == 0 || sym_variant_known(variant), "pair-symmetric variant (R*100 + U*10 + CTAs per SM)");
+    HGB_ARG(min_n >= 0, "min_n");
+    h->sym = variant;
+    h->sym_min_n = min_n;
+    return HGB_OK;
+}
 
 int hgb_set_nbody_mode(int mode) {
     HGB_ARG(mode == HGB_NBODY_EXACT || mode == HGB_NBODY_FAST, "mode");
@@ -113,6 +202,7 @@ int hgb_nbody_destroy(hgb_nbody *h) {
         if (s.vel) cudaFree(s.vel);
         if (s.mass) cudaFree(s.mass);
         if (s.tlist) cudaFree(s.tlist);
+        if (s.sym_ctl) cudaFree(s.sym_ctl);
     }
     delete h;
     return HGB_OK;
@@ -131,6 +221,7 @@ int hgb_nbody_create(hgb_nbody **out, int n, int ngpus) {
     h->npad = h->slice * g;
     h->mode = g_default_mode;
     h->exchange = g_default_exchange;
+    sym_defaults(h);
     h->sh.resize(g);
     for (int i = 0; i < g; ++i) {
         h->sh[i].dev = &rt().devs[i];
@@ -246,6 +337,8 @@ static int nb_advance(hgb_nbody *h, int iterations, float *ms, bool dyn) {
                         s.state[cur], h->npad, h->n, t0, count, nullptr, out, nullptr, d);
                     HGB_LAUNCHED();
                 }
+            } else if (sym_applies(h)) {
+                HGB_TRY(launch_sym(h, s, s.state[cur], out));
             } else {
                 HGB_TRY(launch_step(h, s, s.state[cur], t0, count, nullptr, out, nullptr));
             }

@@ -1,0 +1,288 @@
+// nbody_sym.cuh -- pair-symmetric all-pairs FP64 step for sm_100a (EXACT mode, one GPU).
+//
+// pair_wise_accel (reference src/nbody/nbody-run.c:6-15) is antisymmetric bit for bit:
+// d(j->i) = -d(i->j) exactly, s and the factor are the same doubles, so the contribution of
+// source i to target j is -(d*f) of the pair evaluated from target i's side.  Computing each
+// unordered pair once costs 26 FP64 instructions + one add on each side = 32 per PAIR, i.e. 16
+// per interaction instead of 29.  What has to be kept is accel()'s summation order (reference
+// src/nbody/nbody-run.c:17-25: every target adds its sources j = 0..n-1 in index order; the
+// self pair adds +0 and is skipped, accumulators are never -0).  That makes the step a
+// wavefront:
+//
+//   * worker w (one warp) owns the 32*R targets of block w; lane l owns targets R*l..R*l+R-1
+//     with position and accumulator in registers;
+//   * the sources j < (block start) stream through the warp as a systolic array: at step s lane
+//     l handles source j = s - l, so every lane sees j ascending (its targets' order) and every
+//     source meets the targets i ascending (the source's own order, as a target);
+//   * the partial sum of source j as a target ("chain" accumulator) travels with it: it sits in
+//     a per-warp shared-memory ring next to the source position, each lane subtracts its
+//     R pair forces from it in turn (read-modify-write, __syncwarp between steps);
+//   * the ring is fed tile by tile (one tile = one block of 32*R bodies) from global memory,
+//     where the previous worker left the chain accumulators; `done[tile] == w-1` (release /
+//     acquire) says worker w-1 is through with the tile.  Workers take tickets in index order,
+//     so worker w only ever waits for a worker that is already running: no deadlock, and the
+//     grid is persistent (warps loop over tickets);
+//   * the block's own pairs (the diagonal tile) run through the same skewed schedule with
+//     predicates: j < i evaluates the pair, j == i turns the target's finished lower sum into
+//     the chain accumulator of source j.
+// tests/sym_model.py is a lock-step CPU model of exactly this index logic.
+//
+// The last worker leaves acc[i] = sum_j pair(i, j) in order for every body; a second tiny kernel
+// writes G * acc.  If any operand ever leaves the range of the branch-free IEEE sequences
+// (never for sane finite positions) the kernel raises a flag and the ordinary one-target-per-
+// thread kernel redoes the step from the untouched source state.
+#pragma once
+#include <type_traits>
+
+#include "nbody_kernels.cuh"
+
+namespace hgb {
+
+constexpr int kSymCtlInts = 32;   // ctl[0] = ticket counter, ctl[1] = range flag, done[] follows
+
+__device__ __forceinline__ int sym_ld_acquire(const int *p) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sym_st_release(int *p, int v) {
+    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// d * f of pair_wise_accel for P independent (target, source) pairs, the dependency chains
+// interleaved stage by stage (in-order issue: independent chains must sit next to each other).
+template <int P>
+__device__ __forceinline__ void pair_forces(const double (&px)[P], const double (&py)[P],
+                                            const double (&pz)[P], const double (&xj)[P],
+                                            const double (&yj)[P], const double (&zj)[P],
+                                            double (&vx)[P], double (&vy)[P], double (&vz)[P],
+                                            unsigned &key) {
+    double t[P], y[P], g[P], s[P], a[P], e[P], p[P], q[P];
+#pragma unroll
+    for (int u = 0; u < P; ++u) {
+        vx[u] = __dsub_rn(xj[u], px[u]); vy[u] = __dsub_rn(yj[u], py[u]); vz[u] = __dsub_rn(zj[u], pz[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < P; ++u) {
+        s[u] = __dmul_rn(vx[u], vx[u]); a[u] = __dmul_rn(vy[u], vy[u]); e[u] = __dmul_rn(vz[u], vz[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < P; ++u) s[u] = __dadd_rn(s[u], a[u]);
+#pragma unroll
+    for (int u = 0; u < P; ++u) s[u] = __dadd_rn(s[u], e[u]);
+#pragma unroll
+    for (int u = 0; u < P; ++u) s[u] = __dadd_rn(s[u], kEps);
+#pragma unroll
+    for (int u = 0; u < P; ++u) t[u] = __dmul_rn(s[u], s[u]);
+#pragma unroll
+    for (int u = 0; u < P; ++u) t[u] = __dmul_rn(t[u], s[u]);            // (s*s)*s
+#pragma unroll
+    for (int u = 0; u < P; ++u) { y[u] = mufu_rsqrt(t[u]); key = max(key, range_key(t[u])); }
+#pragma unroll
+    for (int u = 0; u < P; ++u) a[u] = __dmul_rn(y[u], y[u]);
+#pragma unroll
+    for (int u = 0; u < P; ++u) e[u] = __fma_rn(t[u], -a[u], 1.0);
+#pragma unroll
+    for (int u = 0; u < P; ++u) { p[u] = __fma_rn(e[u], 0.375, 0.5); q[u] = __dmul_rn(y[u], e[u]); }
+#pragma unroll
+    for (int u = 0; u < P; ++u) y[u] = __fma_rn(p[u], q[u], y[u]);       // ~1/sqrt(t)
+#pragma unroll
+    for (int u = 0; u < P; ++u) g[u] = __dmul_rn(t[u], y[u]);
+#pragma unroll
+    for (int u = 0; u < P; ++u) e[u] = __fma_rn(-g[u], g[u], t[u]);
+#pragma unroll
+    for (int u = 0; u < P; ++u) g[u] = __fma_rn(e[u], half_of(y[u]), g[u]);  // RN(sqrt(t))
+#pragma unroll
+    for (int u = 0; u < P; ++u) y[u] = odd_up(y[u]);                     // see inv_sqrt_ieee
+#pragma unroll
+    for (int u = 0; u < P; ++u) e[u] = __fma_rn(y[u], -g[u], 1.0);
+#pragma unroll
+    for (int u = 0; u < P; ++u) y[u] = __fma_rn(y[u], e[u], y[u]);
+#pragma unroll
+    for (int u = 0; u < P; ++u) e[u] = __fma_rn(y[u], -g[u], 1.0);
+#pragma unroll
+    for (int u = 0; u < P; ++u) y[u] = __fma_rn(y[u], e[u], y[u]);       // RN(1/g)
+#pragma unroll
+    for (int u = 0; u < P; ++u) {
+        vx[u] = __dmul_rn(vx[u], y[u]); vy[u] = __dmul_rn(vy[u], y[u]); vz[u] = __dmul_rn(vz[u], y[u]);
+    }
+}
+
+constexpr int kSymWarps = 4;   // warps (independent workers) per CTA
+
+// R targets per lane, U systolic steps per unrolled group (R*U independent pair chains in
+// flight per thread), CTAS resident CTAs per SM (register budget).  src: SoA positions with
+// component stride npad (zero beyond n); acc: SoA chain accumulators, same stride.
+template <int R, int U, int CTAS>
+__global__ void __launch_bounds__(kSymWarps * 32, CTAS)
+nbody_sym_kernel(const double *__restrict__ src, int npad, int n, double *acc, int *ctl) {
+    constexpr int BS = 32 * R, RING = 3 * BS;
+    constexpr unsigned FULL = 0xffffffffu;
+    extern __shared__ __align__(16) double sym_smem[];
+    const int lane = threadIdx.x & 31;
+    double *rx = sym_smem + (threadIdx.x >> 5) * 6 * RING;
+    double *ry = rx + RING, *rz = ry + RING, *rax = rz + RING, *ray = rax + RING, *raz = ray + RING;
+    const double *sx = src, *sy = src + npad, *sz = src + 2 * (size_t)npad;
+    double *gax = acc, *gay = acc + npad, *gaz = acc + 2 * (size_t)npad;
+    int *done = ctl + kSymCtlInts;
+    const int T = (n + BS - 1) / BS;
+    unsigned key = 0;
+
+    for (;;) {
+        int w = 0;
+        if (lane == 0) w = atomicAdd(&ctl[0], 1);   // tickets in index order: worker w-1 is already running
+        w = __shfl_sync(FULL, w, 0);
+        if (w >= T) break;
+        const int i0 = w * BS, jend = min(i0 + BS, n), tgt0 = i0 + R * lane;
+        double px[R], py[R], pz[R], ax[R], ay[R], az[R];
+        bool valid[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            px[r] = sx[tgt0 + r]; py[r] = sy[tgt0 + r]; pz[r] = sz[tgt0 + r];
+            ax[r] = 0.0; ay[r] = 0.0; az[r] = 0.0;
+            valid[r] = tgt0 + r < n;
+        }
+        int e = (RING - lane) % RING;   // ring entry of source j = s - lane
+
+        // tile Jt enters the ring: positions always, chain accumulators once worker w-1 released them
+        auto open_tile = [&](int Jt) {
+            const int base = (Jt % 3) * BS, g0 = Jt * BS;
+            const bool lower = Jt < w;
+            if (lower)
+                while (sym_ld_acquire(done + Jt) != w - 1) __nanosleep(64);
+#pragma unroll
+            for (int k = 0; k < R; ++k) {
+                const int idx = lane + 32 * k;
+                rx[base + idx] = sx[g0 + idx]; ry[base + idx] = sy[g0 + idx]; rz[base + idx] = sz[g0 + idx];
+                if (lower) {
+                    rax[base + idx] = __ldcg(gax + g0 + idx);
+                    ray[base + idx] = __ldcg(gay + g0 + idx);
+                    raz[base + idx] = __ldcg(gaz + g0 + idx);
+                }
+            }
+            __syncwarp();
+        };
+        // every lane is through with tile Jt: hand its chain accumulators to worker w+1
+        auto close_tile = [&](int Jt) {
+            const int base = (Jt % 3) * BS, g0 = Jt * BS;
+            __syncwarp();
+#pragma unroll
+            for (int k = 0; k < R; ++k) {
+                const int idx = lane + 32 * k;
+                gax[g0 + idx] = rax[base + idx]; gay[g0 + idx] = ray[base + idx]; gaz[g0 + idx] = raz[base + idx];
+            }
+            __threadfence();
+            __syncwarp();
+            if (lane == 0) sym_st_release(done + Jt, w);
+        };
+        // one predicated step: fill / drain of the systolic skew and the diagonal tile
+        auto slow_step = [&](int s) {
+            const int j = s - lane;
+            if (j >= 0 && j < jend) {
+                const double xj = rx[e], yj = ry[e], zj = rz[e];
+                bool have_u = j < tgt0;   // an earlier lane (or worker) already carries this chain
+                double ux = 0.0, uy = 0.0, uz = 0.0;
+                if (have_u) { ux = rax[e]; uy = ray[e]; uz = raz[e]; }
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const int i = tgt0 + r;
+                    if (i < n) {
+                        if (j == i) {          // lower sum of target i is complete: it becomes j's chain
+                            ux = ax[r]; uy = ay[r]; uz = az[r];
+                            have_u = true;
+                        } else if (j < i) {
+                            double qx[1] = {px[r]}, qy[1] = {py[r]}, qz[1] = {pz[r]};
+                            double jx[1] = {xj}, jy[1] = {yj}, jz[1] = {zj}, vx[1], vy[1], vz[1];
+                            pair_forces<1>(qx, qy, qz, jx, jy, jz, vx, vy, vz, key);
+                            ax[r] = __dadd_rn(ax[r], vx[0]); ay[r] = __dadd_rn(ay[r], vy[0]); az[r] = __dadd_rn(az[r], vz[0]);
+                            ux = __dsub_rn(ux, vx[0]); uy = __dsub_rn(uy, vy[0]); uz = __dsub_rn(uz, vz[0]);
+                        }
+                    }
+                }
+                if (have_u) { rax[e] = ux; ray[e] = uy; raz[e] = uz; }
+            }
+            e = (e + 1 == RING) ? 0 : e + 1;
+            __syncwarp();
+        };
+
+        // U full steps: every lane's source is below the block, no index predicates.  ALLV: the
+        // block has no padding targets (always, unless it is the last block of a ragged n).
+        auto fast_group = [&](auto allv) {
+            constexpr bool ALLV = decltype(allv)::value;
+            int es[U];
+            double qx[R * U], qy[R * U], qz[R * U], jx[R * U], jy[R * U], jz[R * U];
+            double vx[R * U], vy[R * U], vz[R * U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                es[u] = e;
+                e = (e + 1 == RING) ? 0 : e + 1;
+                const double xj = rx[es[u]], yj = ry[es[u]], zj = rz[es[u]];
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    qx[u * R + r] = px[r]; qy[u * R + r] = py[r]; qz[u * R + r] = pz[r];
+                    jx[u * R + r] = xj; jy[u * R + r] = yj; jz[u * R + r] = zj;
+                }
+            }
+            pair_forces<R * U>(qx, qy, qz, jx, jy, jz, vx, vy, vz, key);
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                double ux = rax[es[u]], uy = ray[es[u]], uz = raz[es[u]];
+#pragma unroll
+                for (int r = 0; r < R; ++r) {   // targets ascending: the chain's order
+                    ax[r] = __dadd_rn(ax[r], vx[u * R + r]);
+                    ay[r] = __dadd_rn(ay[r], vy[u * R + r]);
+                    az[r] = __dadd_rn(az[r], vz[u * R + r]);
+                    if (ALLV || valid[r]) {
+                        ux = __dsub_rn(ux, vx[u * R + r]);
+                        uy = __dsub_rn(uy, vy[u * R + r]);
+                        uz = __dsub_rn(uz, vz[u * R + r]);
+                    }
+                }
+                rax[es[u]] = ux; ray[es[u]] = uy; raz[es[u]] = uz;
+                __syncwarp();   // lane l+1 reads this entry in the next step
+            }
+        };
+        const bool full = i0 + BS <= n;
+
+        int s = 0;
+        const int s_end = jend - 1 + 31;
+#pragma unroll 1
+        while (s <= s_end) {
+            if (s % BS == 0 && s / BS <= w) {
+                const int Jt = s / BS;
+                if (Jt >= 2) close_tile(Jt - 2);
+                open_tile(Jt);
+            }
+            const int lim = min(i0, (s / BS + 1) * BS);   // end of the predicate-free run inside this tile
+            if (s >= 31 && s + U <= lim) {
+                if (full) {
+#pragma unroll 1
+                    do { fast_group(std::true_type{}); s += U; } while (s + U <= lim);
+                } else {
+#pragma unroll 1
+                    do { fast_group(std::false_type{}); s += U; } while (s + U <= lim);
+                }
+            } else {
+                slow_step(s);
+                s += 1;
+            }
+        }
+        if (w >= 1) close_tile(w - 1);
+        close_tile(w);   // the block's own chain accumulators; done[w] = w lets worker w+1 in
+    }
+    if (key >= kRangeLimit) ctl[1] = 1;
+}
+
+// buffer[i] = G * acc[i] (reference src/nbody/nbody-run.c:22-24)
+__global__ void nbody_sym_finish_kernel(const double *__restrict__ acc, int npad, int n, PeerOut out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double gx = __dmul_rn(kG, acc[i]), gy = __dmul_rn(kG, acc[(size_t)npad + i]),
+                 gz = __dmul_rn(kG, acc[2 * (size_t)npad + i]);
+    for (int p = 0; p < out.count; ++p) {
+        double *o = out.base[p];
+        o[i] = gx; o[(size_t)npad + i] = gy; o[2 * (size_t)npad + i] = gz;
+    }
+}
+
+}  // namespace hgb

@@ -63,6 +63,13 @@ class NBody:
         check(lib().hgb_nbody_tune(self._h, int(block), int(unroll), int(warps)))
         return self
 
+    def symmetric(self, variant=1, min_n=0):
+        """Pair-symmetric EXACT step (each pair evaluated once, same per-target summation order,
+        bit-identical; hgb_nbody_set_symmetric).  variant 0 = off, 1 = default, else
+        R*100 + U*10 + CTAs per SM; applies to one-GPU handles with n >= min_n."""
+        check(lib().hgb_nbody_set_symmetric(self._h, int(variant), int(min_n)))
+        return self
+
     def upload(self, pos):
         _bodies(pos, "pos")
         assert pos.shape[0] == self.n

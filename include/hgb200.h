@@ -86,6 +86,13 @@ int hgb_nbody_config(hgb_nbody *h, int mode, int exchange);
 /* kernel variant; 0 = default: threads per CTA {128,256}, sources per unrolled group/2 {1,2,4},
  * resident warps per SM the register allocation allows {24,28,32,40} (28: 128-thread CTAs only) */
 int hgb_nbody_tune(hgb_nbody *h, int block, int unroll, int warps);
+/* Pair-symmetric EXACT step (csrc/nbody_sym.cuh): every unordered pair is evaluated once and added to
+ * both bodies, each target still summing its sources in the order of accel() (src/nbody/nbody-run.c:
+ * 17-25), so the result is bit-identical to hgb_nbody_tune's kernel at 16 instead of 29 FP64
+ * instructions per interaction.  variant: 0 = off, 1 = default, else R*100 + U*10 + CTAs per SM;
+ * used on single-GPU handles in EXACT mode when n >= min_n (the wavefront needs a large n to fill
+ * the GPU).  New handles take their default from env HGB_NBODY_SYM / HGB_NBODY_SYM_MIN_N. */
+int hgb_nbody_set_symmetric(hgb_nbody *h, int variant, int min_n);
 int hgb_nbody_upload(hgb_nbody *h, const double *pos_aos);       /* all n bodies */
 /* `iterations` steps; *ms (may be NULL) = device time, CUDA events, max over local devices */
 int hgb_nbody_step(hgb_nbody *h, int iterations, float *ms);
