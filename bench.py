@@ -31,6 +31,7 @@ CONV_TIMED = 100         # device-resident timing runs 10 x 10 iterations back t
                          # iterations last ~1 ms, comparable to the host skew between ranks after a barrier
 FLOP_PER_INTERACTION = 19          # 3 sub, 3 mul+3 add (+EPS), 2 mul, sqrt, div, 3 mul+3 add
 FP64_INSTR_PER_INTERACTION = 29    # exact mode: 17 plain + 8 (IEEE sqrt) + 4 (IEEE reciprocal) FP64-pipe ops (tools/sass_loop.py)
+FP64_INSTR_PER_INTERACTION_SYM = 16  # pair-symmetric kernel: 26 + 3 + 3 FP64-pipe ops per PAIR = 2 interactions
 BYTES_PER_PIXEL = 16               # 8 B read + 8 B written per inner pixel per iteration
 
 
@@ -252,6 +253,9 @@ def main():
     # ---------------- nbody: device-resident steps -------------------------------------------
     nb = H.nbody.NBody(n, ngpus=None, mode=H.NBODY_EXACT)
     nb.upload(pos_np)
+    sym = int(L.hgb_nbody_symmetric(nb._h))      # pair-symmetric variant in use (0: standard kernel)
+    fp64_instr = FP64_INSTR_PER_INTERACTION_SYM if sym else FP64_INSTR_PER_INTERACTION
+    nb_kernel = f"nbody_sym_kernel<{sym // 100},{sym // 10 % 10},{sym % 10}>" if sym else "nbody_step_kernel<128,2,24,false>"
     for _ in range(args.warmup):
         nb.step(1)
     sampler = ClockSampler(local_rank)
@@ -355,6 +359,7 @@ def main():
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
             "config": {"workload": f"nbody N={n} uniform cube seed 1, all-pairs FP64, EXACT mode (bit-identical to the reference), BASELINE configs[3]",
+                       "kernel": nb_kernel,
                        "parallelism": f"targets sharded over {world} GPU(s), ncclAllGather of positions per step",
                        "l2": "512 MiB fill between timed steps (nbody); convolution inputs (2 GiB) exceed L2",
                        "timing": "CUDA events on the library stream per step, max over ranks"},
@@ -367,12 +372,13 @@ def main():
             "clocks": clocks,
             "roofline": {"bound": "fp64", "achieved": value / world * FLOP_PER_INTERACTION / 1e12, "peak": tf.value,
                          "unit": "TFLOP/s", "frac": value / world * FLOP_PER_INTERACTION / 1e12 / tf.value,
-                         "traffic": ncu_traffic("nbody_step_kernel<"),
+                         "kernel": nb_kernel,
+                         "traffic": ncu_traffic("nbody_sym_kernel<" if sym else "nbody_step_kernel<"),
                          "traffic_note": "ncu dram bytes per launch (profiles/ncu_traffic.json): the 24 MiB of positions stay in L2",
                          "per_gpu": True,
                          "peak_source": "in-run dependent-free DFMA probe (MEASURED_PEAKS.json has no FP64 figure)",
-                         "fp64_pipe_util": value / world * FP64_INSTR_PER_INTERACTION / (tf.value / 2 * 1e12),
-                         "fp64_pipe_util_note": f"{FP64_INSTR_PER_INTERACTION} FP64-pipe instructions per interaction in exact mode (SASS count) vs measured DFMA issue rate",
+                         "fp64_pipe_util": value / world * fp64_instr / (tf.value / 2 * 1e12),
+                         "fp64_pipe_util_note": f"{fp64_instr} FP64-pipe instructions per interaction in exact mode (SASS count) vs measured DFMA issue rate",
                          "probe_sm_mhz": mhz.value, "hbm_copy_probe_gbs": gbs.value},
             "conv": conv,
         }

@@ -178,6 +178,8 @@ int hgb_nbody_set_symmetric(hgb_nbody *h, int variant, int min_n) {
     return HGB_OK;
 }
 
+int hgb_nbody_symmetric(const hgb_nbody *h) { return h && sym_applies(h) ? h->sym : 0; }
+
 int hgb_set_nbody_mode(int mode) {
     HGB_ARG(mode == HGB_NBODY_EXACT || mode == HGB_NBODY_FAST, "mode");
     g_default_mode = mode;

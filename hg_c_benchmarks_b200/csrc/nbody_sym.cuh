@@ -171,7 +171,7 @@ nbody_sym_kernel(const double *__restrict__ src, int npad, int n, double *acc, i
                 const int idx = lane + 32 * k;
                 gax[g0 + idx] = rax[base + idx]; gay[g0 + idx] = ray[base + idx]; gaz[g0 + idx] = raz[base + idx];
             }
-            __threadfence();
+            asm volatile("fence.acq_rel.gpu;" ::: "memory");   // each lane's stores before the flag
             __syncwarp();
             if (lane == 0) sym_st_release(done + Jt, w);
         };

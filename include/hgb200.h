@@ -93,6 +93,8 @@ int hgb_nbody_tune(hgb_nbody *h, int block, int unroll, int warps);
  * used on single-GPU handles in EXACT mode when n >= min_n (the wavefront needs a large n to fill
  * the GPU).  New handles take their default from env HGB_NBODY_SYM / HGB_NBODY_SYM_MIN_N. */
 int hgb_nbody_set_symmetric(hgb_nbody *h, int variant, int min_n);
+/* the variant hgb_nbody_step will use on this handle as configured now (0: the standard kernel) */
+int hgb_nbody_symmetric(const hgb_nbody *h);
 int hgb_nbody_upload(hgb_nbody *h, const double *pos_aos);       /* all n bodies */
 /* `iterations` steps; *ms (may be NULL) = device time, CUDA events, max over local devices */
 int hgb_nbody_step(hgb_nbody *h, int iterations, float *ms);
