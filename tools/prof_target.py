@@ -1,5 +1,5 @@
 """Short profiling target for ncu --set full: one nbody step (EXACT and FAST) and a few
-convolution iterations.  Usage: python tools/prof_target.py [nbody|conv]"""
+convolution iterations.  Usage: python tools/prof_target.py [nbody|sym|conv]"""
 import os
 import sys
 
@@ -15,6 +15,14 @@ if what == "nbody":
     with H.nbody.NBody(n, mode=H.NBODY_EXACT) as nb:
         nb.upload(pos)
         print("EXACT ms", nb.step(1))
+elif what == "sym":
+    # pair-symmetric kernel: python tools/prof_target.py sym <variant> [n]
+    variant = int(sys.argv[2]) if len(sys.argv) > 2 else 1
+    n = int(sys.argv[3]) if len(sys.argv) > 3 else 1048576
+    pos = synth.uniform_cube(n, seed=1)
+    with H.nbody.NBody(n, mode=H.NBODY_EXACT) as nb:
+        nb.symmetric(variant, 0).upload(pos)
+        print("SYM", variant, "ms", nb.step(1))
 else:
     n = 16384
     dense = synth.image_float(n, n, seed=3)
