@@ -82,12 +82,12 @@ static int launch_step(const hgb_nbody *h, const NbShard &s, const double *src, 
 
 // ---- pair-symmetric step (nbody_sym.cuh): one GPU, EXACT mode, all n targets --------------
 static int g_default_sym = -1, g_default_sym_min_n = -1;   // -1: read HGB_NBODY_SYM / HGB_NBODY_SYM_MIN_N
-constexpr int kSymDefaultVariant = 224;                    // R = 2, U = 2, 4 CTAs (16 warps) per SM
+constexpr int kSymDefaultVariant = 423;                    // R = 4, U = 2, 3 CTAs (12 warps) per SM
 constexpr int kSymDefaultMinN = 262144;                    // below this the wavefront ramp dominates
 
 static bool sym_variant_known(int v) {
     switch (v) {
-        case 124: case 146: case 148: case 216: case 224: case 225: case 226: case 234: case 413: case 423:
+        case 124: case 146: case 148: case 224: case 226: case 228: case 243: case 413: case 423: case 422:
             return true;
     }
     return false;
@@ -95,7 +95,7 @@ static bool sym_variant_known(int v) {
 
 template <int R, int U, int CTAS>
 static int launch_sym_variant(cudaStream_t st, int sms, const double *src, int npad, int n, double *acc, int *ctl) {
-    const size_t smem = (size_t)kSymWarps * 6 * 3 * 32 * R * sizeof(double);
+    const size_t smem = (size_t)kSymWarps * 6 * 3 * 32 * sizeof(double);   // per warp: 6 arrays x 3 chunks of 32
     static bool attr_set = false;   // per instantiation
     if (!attr_set) {
         HGB_CUDA(cudaFuncSetAttribute(nbody_sym_kernel<R, U, CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -114,18 +114,18 @@ static bool sym_applies(const hgb_nbody *h) {
 // whole step on shard s: tickets/flags reset, wavefront kernel, G*acc, conditional redo
 static int launch_sym(const hgb_nbody *h, NbShard &s, const double *src, const PeerOut &out) {
     cudaStream_t st = s.dev->stream;
-    const int R = h->sym / 100, tiles = (h->n + 32 * R - 1) / (32 * R);
+    const int chunks = (h->n + 31) / 32;
     if (!s.sym_ctl) HGB_CUDA(cudaMalloc(&s.sym_ctl, sizeof(int) * (kSymCtlInts + h->npad / 32 + 1)));
     HGB_CUDA(cudaMemsetAsync(s.sym_ctl, 0, sizeof(int) * kSymCtlInts, st));
-    HGB_CUDA(cudaMemsetAsync(s.sym_ctl + kSymCtlInts, 0xFF, sizeof(int) * tiles, st));   // done[] = -1
+    HGB_CUDA(cudaMemsetAsync(s.sym_ctl + kSymCtlInts, 0xFF, sizeof(int) * chunks, st));   // done[] = -1
     int sms = 0;
     HGB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s.dev->device));
     double *acc = s.stage;   // the AoS staging buffer is idle between upload and download
     int rc = HGB_ERR_ARG;
     switch (h->sym) {
 #define HGB_SYM(R_, U_, C_) case R_ * 100 + U_ * 10 + C_: rc = launch_sym_variant<R_, U_, C_>(st, sms, src, h->npad, h->n, acc, s.sym_ctl); break;
-        HGB_SYM(1, 2, 4) HGB_SYM(1, 4, 6) HGB_SYM(1, 4, 8) HGB_SYM(2, 1, 6) HGB_SYM(2, 2, 4) HGB_SYM(2, 2, 5)
-        HGB_SYM(2, 2, 6) HGB_SYM(2, 3, 4) HGB_SYM(4, 1, 3) HGB_SYM(4, 2, 3)
+        HGB_SYM(1, 2, 4) HGB_SYM(1, 4, 6) HGB_SYM(1, 4, 8) HGB_SYM(2, 2, 4) HGB_SYM(2, 2, 6) HGB_SYM(2, 2, 8)
+        HGB_SYM(2, 4, 3) HGB_SYM(4, 1, 3) HGB_SYM(4, 2, 3) HGB_SYM(4, 2, 2)
 #undef HGB_SYM
         default: set_error("no pair-symmetric nbody variant %d", h->sym);
     }

@@ -17,12 +17,14 @@
 //   * the partial sum of source j as a target ("chain" accumulator) travels with it: it sits in
 //     a per-warp shared-memory ring next to the source position, each lane subtracts its
 //     R pair forces from it in turn (read-modify-write, __syncwarp between steps);
-//   * the ring is fed tile by tile (one tile = one block of 32*R bodies) from global memory,
-//     where the previous worker left the chain accumulators; `done[tile] == w-1` (release /
-//     acquire) says worker w-1 is through with the tile.  Workers take tickets in index order,
+//   * the ring (three chunks of 32 sources) is fed chunk by chunk from global memory, where the
+//     previous worker left the chain accumulators; `done[chunk] == w-1` (release / acquire) says
+//     worker w-1 is through with the chunk, two chunks (64 steps) after it took it in -- the
+//     minimum distance between consecutive workers, which is what bounds the wavefront's
+//     parallelism (N / (128 * resident warps) must stay well above 1).  Workers take tickets in index order,
 //     so worker w only ever waits for a worker that is already running: no deadlock, and the
 //     grid is persistent (warps loop over tickets);
-//   * the block's own pairs (the diagonal tile) run through the same skewed schedule with
+//   * the block's own pairs (the diagonal chunks) run through the same skewed schedule with
 //     predicates: j < i evaluates the pair, j == i turns the target's finished lower sum into
 //     the chain accumulator of source j.
 // tests/sym_model.py is a lock-step CPU model of exactly this index logic.
@@ -116,7 +118,7 @@ constexpr int kSymWarps = 4;   // warps (independent workers) per CTA
 template <int R, int U, int CTAS>
 __global__ void __launch_bounds__(kSymWarps * 32, CTAS)
 nbody_sym_kernel(const double *__restrict__ src, int npad, int n, double *acc, int *ctl) {
-    constexpr int BS = 32 * R, RING = 3 * BS;
+    constexpr int BS = 32 * R, CH = 32, RING = 3 * CH;   // block of targets, hand-off chunk, ring entries
     constexpr unsigned FULL = 0xffffffffu;
     extern __shared__ __align__(16) double sym_smem[];
     const int lane = threadIdx.x & 31;
@@ -144,38 +146,29 @@ nbody_sym_kernel(const double *__restrict__ src, int npad, int n, double *acc, i
         }
         int e = (RING - lane) % RING;   // ring entry of source j = s - lane
 
-        // tile Jt enters the ring: positions always, chain accumulators once worker w-1 released them
-        auto open_tile = [&](int Jt) {
-            const int base = (Jt % 3) * BS, g0 = Jt * BS;
-            const bool lower = Jt < w;
+        // chunk c (32 sources) enters the ring: positions always, chain accumulators once worker w-1
+        // released them (chunks of the block itself get theirs from the owning lanes)
+        auto open_chunk = [&](int c) {
+            const int slot = (c % 3) * CH + lane, g = c * CH + lane;
+            const bool lower = c < w * R;
             if (lower)
-                while (sym_ld_acquire(done + Jt) != w - 1) __nanosleep(64);
-#pragma unroll
-            for (int k = 0; k < R; ++k) {
-                const int idx = lane + 32 * k;
-                rx[base + idx] = sx[g0 + idx]; ry[base + idx] = sy[g0 + idx]; rz[base + idx] = sz[g0 + idx];
-                if (lower) {
-                    rax[base + idx] = __ldcg(gax + g0 + idx);
-                    ray[base + idx] = __ldcg(gay + g0 + idx);
-                    raz[base + idx] = __ldcg(gaz + g0 + idx);
-                }
+                while (sym_ld_acquire(done + c) != w - 1) __nanosleep(32);
+            rx[slot] = sx[g]; ry[slot] = sy[g]; rz[slot] = sz[g];
+            if (lower) {
+                rax[slot] = __ldcg(gax + g); ray[slot] = __ldcg(gay + g); raz[slot] = __ldcg(gaz + g);
             }
             __syncwarp();
         };
-        // every lane is through with tile Jt: hand its chain accumulators to worker w+1
-        auto close_tile = [&](int Jt) {
-            const int base = (Jt % 3) * BS, g0 = Jt * BS;
+        // every lane is through with chunk c: hand its chain accumulators to worker w+1.  The warp
+        // barrier orders the lanes' stores before lane 0's release (cumulative), as in a grid barrier.
+        auto close_chunk = [&](int c) {
+            const int slot = (c % 3) * CH + lane, g = c * CH + lane;
             __syncwarp();
-#pragma unroll
-            for (int k = 0; k < R; ++k) {
-                const int idx = lane + 32 * k;
-                gax[g0 + idx] = rax[base + idx]; gay[g0 + idx] = ray[base + idx]; gaz[g0 + idx] = raz[base + idx];
-            }
-            asm volatile("fence.acq_rel.gpu;" ::: "memory");   // each lane's stores before the flag
+            gax[g] = rax[slot]; gay[g] = ray[slot]; gaz[g] = raz[slot];
             __syncwarp();
-            if (lane == 0) sym_st_release(done + Jt, w);
+            if (lane == 0) sym_st_release(done + c, w);
         };
-        // one predicated step: fill / drain of the systolic skew and the diagonal tile
+        // one predicated step: fill / drain of the systolic skew and the diagonal chunks
         auto slow_step = [&](int s) {
             const int j = s - lane;
             if (j >= 0 && j < jend) {
@@ -245,15 +238,15 @@ nbody_sym_kernel(const double *__restrict__ src, int npad, int n, double *acc, i
         const bool full = i0 + BS <= n;
 
         int s = 0;
-        const int s_end = jend - 1 + 31;
+        const int s_end = jend - 1 + 31, last_chunk = (jend - 1) / CH;
 #pragma unroll 1
         while (s <= s_end) {
-            if (s % BS == 0 && s / BS <= w) {
-                const int Jt = s / BS;
-                if (Jt >= 2) close_tile(Jt - 2);
-                open_tile(Jt);
+            if (s % CH == 0 && s / CH <= last_chunk) {
+                const int c = s / CH;
+                if (c >= 2) close_chunk(c - 2);   // lane 31 left it 2 steps ago at the latest
+                open_chunk(c);
             }
-            const int lim = min(i0, (s / BS + 1) * BS);   // end of the predicate-free run inside this tile
+            const int lim = min(i0, (s / CH + 1) * CH);   // end of the predicate-free run inside this chunk
             if (s >= 31 && s + U <= lim) {
                 if (full) {
 #pragma unroll 1
@@ -267,8 +260,8 @@ nbody_sym_kernel(const double *__restrict__ src, int npad, int n, double *acc, i
                 s += 1;
             }
         }
-        if (w >= 1) close_tile(w - 1);
-        close_tile(w);   // the block's own chain accumulators; done[w] = w lets worker w+1 in
+        if (last_chunk >= 1) close_chunk(last_chunk - 1);
+        close_chunk(last_chunk);   // done[c] = w for the block's own chunks lets worker w+1 in
     }
     if (key >= kRangeLimit) ctl[1] = 1;
 }

@@ -1,7 +1,7 @@
 """Lock-step Python model of the pair-symmetric nbody schedule (csrc/nbody_sym.cuh).
 
 Test infrastructure: it mirrors, loop for loop, the index logic of `nbody_sym_kernel`
-(systolic skew over the 32 lanes, three-slot ring, open/close of source tiles, the diagonal
+(systolic skew over the 32 lanes, three-chunk ring, open/close of source chunks, the diagonal
 block, partial last block) with Python floats (IEEE binary64, one rounding per operator), so
 the schedule can be checked on a CPU against the plain in-order sum of the reference
 (`accel`, reference src/nbody/nbody-run.c:17-25): every target must receive exactly the same
@@ -15,6 +15,7 @@ import math
 G = 9.8      # reference src/nbody/nbody-run.h:12
 EPS = 0.005  # reference src/nbody/nbody-run.h:13
 LANES = 32
+CH = 32     # sources per hand-off chunk
 
 
 def pair(px, py, pz, xj, yj, zj):
@@ -47,31 +48,33 @@ class SymModel:
         self.y = [p[1] for p in pos] + [0.0] * (npad - self.n)
         self.z = [p[2] for p in pos] + [0.0] * (npad - self.n)
         self.acc = [[None] * npad for _ in range(3)]   # global accumulator chain (SoA)
-        self.done = [-1] * self.T                      # done[Jt] = last worker that closed tile Jt
+        self.nchunks = (self.n + CH - 1) // CH
+        self.done = [-1] * self.nchunks                # done[c] = last worker that closed chunk c
         self.fast_steps = self.slow_steps = 0
 
-    # -- tile traffic -------------------------------------------------------------------
-    def open(self, w, Jt, ring):
-        BS, base = self.BS, (Jt % 3) * self.BS
-        if Jt < w:
-            assert self.done[Jt] == w - 1, (w, Jt, self.done[Jt])
-        for idx in range(BS):
-            g = Jt * BS + idx
+    # -- chunk traffic (one chunk = 32 sources, the hand-off unit between workers) -------------
+    def open(self, w, c, ring):
+        base = (c % 3) * CH
+        lower = c < w * self.R
+        if lower:
+            assert self.done[c] == w - 1, (w, c, self.done[c])
+        for idx in range(CH):
+            g = c * CH + idx
             ring[0][base + idx], ring[1][base + idx], ring[2][base + idx] = self.x[g], self.y[g], self.z[g]
-            for c in range(3):
-                ring[3 + c][base + idx] = self.acc[c][g] if Jt < w else None
+            for k in range(3):
+                ring[3 + k][base + idx] = self.acc[k][g] if lower else None
 
-    def close(self, w, Jt, ring):
-        BS, base = self.BS, (Jt % 3) * self.BS
-        for idx in range(BS):
-            for c in range(3):
-                self.acc[c][Jt * BS + idx] = ring[3 + c][base + idx]
-        self.done[Jt] = w
+    def close(self, w, c, ring):
+        base = (c % 3) * CH
+        for idx in range(CH):
+            for k in range(3):
+                self.acc[k][c * CH + idx] = ring[3 + k][base + idx]
+        self.done[c] = w
 
     # -- one worker = one warp ----------------------------------------------------------
     def worker(self, w):
         R, U, BS, n = self.R, self.U, self.BS, self.n
-        RING = 3 * BS
+        RING = 3 * CH
         i0 = w * BS
         jend = min(i0 + BS, n)
         ring = [[None] * RING for _ in range(6)]
@@ -115,28 +118,30 @@ class SymModel:
                         ring[3][e[l]], ring[4][e[l]], ring[5][e[l]] = u
                 e[l] = 0 if e[l] + 1 == RING else e[l] + 1
 
-        s, s_end = 0, jend - 1 + (LANES - 1)
+        s, s_end, last_chunk = 0, jend - 1 + (LANES - 1), (jend - 1) // CH
         while s <= s_end:
-            if s % BS == 0 and s // BS <= w:
-                Jt = s // BS
-                if Jt >= 2:
-                    self.close(w, Jt - 2, ring)
-                self.open(w, Jt, ring)
-            if s >= LANES - 1 and s + U <= i0 and (s % BS) + U <= BS:
-                for u_ in range(U):
-                    fast_step(s + u_)
-                self.fast_steps += U
-                s += U
+            if s % CH == 0 and s // CH <= last_chunk:
+                c = s // CH
+                if c >= 2:
+                    self.close(w, c - 2, ring)
+                self.open(w, c, ring)
+            lim = min(i0, (s // CH + 1) * CH)
+            if s >= LANES - 1 and s + U <= lim:
+                while s + U <= lim:
+                    for u_ in range(U):
+                        fast_step(s + u_)
+                    self.fast_steps += U
+                    s += U
             else:
                 slow_step(s)
                 self.slow_steps += 1
                 s += 1
-        if w >= 1:
-            self.close(w, w - 1, ring)
-        self.close(w, w, ring)
+        if last_chunk >= 1:
+            self.close(w, last_chunk - 1, ring)
+        self.close(w, last_chunk, ring)
 
     def step(self):
         for w in range(self.T):
             self.worker(w)
-        assert self.done == [self.T - 1] * self.T
+        assert self.done == [self.T - 1] * self.nchunks
         return [(G * self.acc[0][i], G * self.acc[1][i], G * self.acc[2][i]) for i in range(self.n)]

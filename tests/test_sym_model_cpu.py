@@ -10,8 +10,8 @@ from sym_model import SymModel, reference_step
 
 
 @pytest.mark.parametrize("n,R,U", [(1, 2, 2), (3, 2, 2), (63, 2, 2), (64, 2, 2), (65, 2, 2), (200, 2, 2),
-                                   (333, 2, 2), (300, 1, 2), (300, 1, 4), (257, 2, 1), (450, 2, 3),
-                                   (300, 4, 1), (420, 4, 2)])
+                                   (333, 2, 2), (300, 1, 2), (300, 1, 4), (257, 2, 1), (450, 2, 4),
+                                   (300, 4, 1), (420, 4, 2), (129, 4, 2)])
 def test_schedule_reproduces_the_in_order_sum(n, R, U):
     from oracle import port
     pos = synth.uniform_cube(n, seed=n)
