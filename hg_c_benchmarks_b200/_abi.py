@@ -46,6 +46,7 @@ SIGNATURES = {
     "hgb_nbody_tune": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int]),
     "hgb_nbody_set_symmetric": (C.c_int, [_vp, C.c_int, C.c_int]),
     "hgb_nbody_symmetric": (C.c_int, [_vp]),
+    "hgb_nbody_sym_counters": (C.c_int, [_vp, C.POINTER(C.c_ulonglong)]),
     "hgb_nbody_upload": (C.c_int, [_vp, _dp]),
     "hgb_nbody_step": (C.c_int, [_vp, C.c_int, _fp]),
     "hgb_nbody_download": (C.c_int, [_vp, _dp, _dp]),

@@ -87,22 +87,22 @@ constexpr int kSymDefaultMinN = 262144;                    // below this the wav
 
 static bool sym_variant_known(int v) {
     switch (v) {
-        case 124: case 146: case 148: case 224: case 226: case 228: case 243: case 413: case 423: case 422:
+        case 124: case 146: case 148: case 224: case 226: case 228: case 243: case 413: case 423: case 422: case 1226: case 1423:
             return true;
     }
     return false;
 }
 
-template <int R, int U, int CTAS>
+template <int R, int U, int CTAS, bool PROF = false>
 static int launch_sym_variant(cudaStream_t st, int sms, const double *src, int npad, int n, double *acc, int *ctl) {
     const size_t smem = (size_t)kSymWarps * 6 * 3 * 32 * sizeof(double);   // per warp: 6 arrays x 3 chunks of 32
     static bool attr_set = false;   // per instantiation
     if (!attr_set) {
-        HGB_CUDA(cudaFuncSetAttribute(nbody_sym_kernel<R, U, CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        HGB_CUDA(cudaFuncSetAttribute(nbody_sym_kernel<R, U, CTAS, PROF>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)smem));
         attr_set = true;
     }
-    nbody_sym_kernel<R, U, CTAS><<<sms * CTAS, kSymWarps * 32, smem, st>>>(src, npad, n, acc, ctl);
+    nbody_sym_kernel<R, U, CTAS, PROF><<<sms * CTAS, kSymWarps * 32, smem, st>>>(src, npad, n, acc, ctl);
     HGB_LAUNCHED();
     return HGB_OK;
 }
@@ -115,6 +115,7 @@ static bool sym_applies(const hgb_nbody *h) {
 static int launch_sym(const hgb_nbody *h, NbShard &s, const double *src, const PeerOut &out) {
     cudaStream_t st = s.dev->stream;
     const int chunks = (h->n + 31) / 32;
+    (void)0;
     if (!s.sym_ctl) HGB_CUDA(cudaMalloc(&s.sym_ctl, sizeof(int) * (kSymCtlInts + h->npad / 32 + 1)));
     HGB_CUDA(cudaMemsetAsync(s.sym_ctl, 0, sizeof(int) * kSymCtlInts, st));
     HGB_CUDA(cudaMemsetAsync(s.sym_ctl + kSymCtlInts, 0xFF, sizeof(int) * chunks, st));   // done[] = -1
@@ -127,6 +128,9 @@ static int launch_sym(const hgb_nbody *h, NbShard &s, const double *src, const P
         HGB_SYM(1, 2, 4) HGB_SYM(1, 4, 6) HGB_SYM(1, 4, 8) HGB_SYM(2, 2, 4) HGB_SYM(2, 2, 6) HGB_SYM(2, 2, 8)
         HGB_SYM(2, 4, 3) HGB_SYM(4, 1, 3) HGB_SYM(4, 2, 3) HGB_SYM(4, 2, 2)
 #undef HGB_SYM
+        // diagnostic instantiations (clock64 spans -> hgb_nbody_sym_counters): variant + 1000
+        case 1226: rc = launch_sym_variant<2, 2, 6, true>(st, sms, src, h->npad, h->n, acc, s.sym_ctl); break;
+        case 1423: rc = launch_sym_variant<4, 2, 3, true>(st, sms, src, h->npad, h->n, acc, s.sym_ctl); break;
         default: set_error("no pair-symmetric nbody variant %d", h->sym);
     }
     HGB_TRY(rc);
@@ -179,6 +183,16 @@ int hgb_nbody_set_symmetric(hgb_nbody *h, int variant, int min_n) {
 }
 
 int hgb_nbody_symmetric(const hgb_nbody *h) { return h && sym_applies(h) ? h->sym : 0; }
+
+int hgb_nbody_sym_counters(hgb_nbody *h, unsigned long long *out7) {
+    HGB_ARG(h && out7, "handle / out");
+    NbShard &s = h->sh[0];
+    if (!s.sym_ctl) { set_error("the pair-symmetric kernel has not run on this handle"); return HGB_ERR_STATE; }
+    HGB_CUDA(cudaSetDevice(s.dev->device));
+    HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
+    HGB_CUDA(cudaMemcpy(out7, s.sym_ctl + 8, 7 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    return HGB_OK;
+}
 
 int hgb_set_nbody_mode(int mode) {
     HGB_ARG(mode == HGB_NBODY_EXACT || mode == HGB_NBODY_FAST, "mode");

@@ -115,11 +115,14 @@ constexpr int kSymWarps = 4;   // warps (independent workers) per CTA
 // R targets per lane, U systolic steps per unrolled group (R*U independent pair chains in
 // flight per thread), CTAS resident CTAs per SM (register budget).  src: SoA positions with
 // component stride npad (zero beyond n); acc: SoA chain accumulators, same stride.
-template <int R, int U, int CTAS>
+// PROF: lane 0 of every warp accumulates clock64() spans (flag wait, chunk loads, chunk release, the
+// predicate-free loop, predicated steps, whole workers) into ctl[8..] -- a diagnostic instantiation.
+template <int R, int U, int CTAS, bool PROF = false>
 __global__ void __launch_bounds__(kSymWarps * 32, CTAS)
 nbody_sym_kernel(const double *__restrict__ src, int npad, int n, double *acc, int *ctl) {
     constexpr int BS = 32 * R, CH = 32, RING = 3 * CH;   // block of targets, hand-off chunk, ring entries
     constexpr unsigned FULL = 0xffffffffu;
+    static_assert(CH % U == 0, "groups of U steps must not straddle a chunk boundary");
     extern __shared__ __align__(16) double sym_smem[];
     const int lane = threadIdx.x & 31;
     double *rx = sym_smem + (threadIdx.x >> 5) * 6 * RING;
@@ -129,8 +132,11 @@ nbody_sym_kernel(const double *__restrict__ src, int npad, int n, double *acc, i
     int *done = ctl + kSymCtlInts;
     const int T = (n + BS - 1) / BS;
     unsigned key = 0;
+    long long t_wait = 0, t_open = 0, t_close = 0, t_fast = 0, t_slow = 0, t_work = 0, n_chunks = 0;
+    auto now = [] { return PROF ? clock64() : 0ll; };
 
     for (;;) {
+        const long long w_begin = now();
         int w = 0;
         if (lane == 0) w = atomicAdd(&ctl[0], 1);   // tickets in index order: worker w-1 is already running
         w = __shfl_sync(FULL, w, 0);
@@ -151,51 +157,79 @@ nbody_sym_kernel(const double *__restrict__ src, int npad, int n, double *acc, i
         auto open_chunk = [&](int c) {
             const int slot = (c % 3) * CH + lane, g = c * CH + lane;
             const bool lower = c < w * R;
+            const long long a0 = now();
             if (lower)
                 while (sym_ld_acquire(done + c) != w - 1) __nanosleep(32);
+            const long long a1 = now();
             rx[slot] = sx[g]; ry[slot] = sy[g]; rz[slot] = sz[g];
             if (lower) {
                 rax[slot] = __ldcg(gax + g); ray[slot] = __ldcg(gay + g); raz[slot] = __ldcg(gaz + g);
             }
             __syncwarp();
+            if (PROF) { t_wait += a1 - a0; t_open += now() - a1; ++n_chunks; }
         };
         // every lane is through with chunk c: hand its chain accumulators to worker w+1.  The warp
         // barrier orders the lanes' stores before lane 0's release (cumulative), as in a grid barrier.
         auto close_chunk = [&](int c) {
             const int slot = (c % 3) * CH + lane, g = c * CH + lane;
+            const long long a0 = now();
             __syncwarp();
             gax[g] = rax[slot]; gay[g] = ray[slot]; gaz[g] = raz[slot];
             __syncwarp();
             if (lane == 0) sym_st_release(done + c, w);
+            if (PROF) { __syncwarp(); t_close += now() - a0; }
         };
-        // one predicated step: fill / drain of the systolic skew and the diagonal chunks
-        auto slow_step = [&](int s) {
-            const int j = s - lane;
-            if (j >= 0 && j < jend) {
-                const double xj = rx[e], yj = ry[e], zj = rz[e];
-                bool have_u = j < tgt0;   // an earlier lane (or worker) already carries this chain
+        // U predicated steps starting at step s0 (a multiple of U, so the group stays inside one chunk):
+        // fill / drain of the systolic skew and the diagonal chunks.  These steps are the critical
+        // path of the wavefront (worker w+1 cannot enter its own block before worker w left its), so
+        // all R*U pairs are evaluated unconditionally and interleaved like the predicate-free path;
+        // the predicates only select what is added (j < i), what starts a chain (j == i) and what is
+        // dropped (j > i, padding targets, lanes outside the stream: those read a zero source).
+        auto edge_group = [&](int s0) {
+            int es[U];
+            double qx[R * U], qy[R * U], qz[R * U], jx[R * U], jy[R * U], jz[R * U];
+            double vx[R * U], vy[R * U], vz[R * U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                es[u] = e;
+                e = (e + 1 == RING) ? 0 : e + 1;
+                const int j = s0 + u - lane;
+                const bool act = j >= 0 && j < jend;
+                const double xj = act ? rx[es[u]] : 0.0, yj = act ? ry[es[u]] : 0.0, zj = act ? rz[es[u]] : 0.0;
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    qx[u * R + r] = px[r]; qy[u * R + r] = py[r]; qz[u * R + r] = pz[r];
+                    jx[u * R + r] = xj; jy[u * R + r] = yj; jz[u * R + r] = zj;
+                }
+            }
+            pair_forces<R * U>(qx, qy, qz, jx, jy, jz, vx, vy, vz, key);
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int j = s0 + u - lane;
+                const bool act = j >= 0 && j < jend;
+                bool have_u = act && j < tgt0;   // an earlier lane (or worker) already carries this chain
                 double ux = 0.0, uy = 0.0, uz = 0.0;
-                if (have_u) { ux = rax[e]; uy = ray[e]; uz = raz[e]; }
+                if (have_u) { ux = rax[es[u]]; uy = ray[es[u]]; uz = raz[es[u]]; }
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
                     const int i = tgt0 + r;
-                    if (i < n) {
+                    if (act && i < n) {
                         if (j == i) {          // lower sum of target i is complete: it becomes j's chain
                             ux = ax[r]; uy = ay[r]; uz = az[r];
                             have_u = true;
                         } else if (j < i) {
-                            double qx[1] = {px[r]}, qy[1] = {py[r]}, qz[1] = {pz[r]};
-                            double jx[1] = {xj}, jy[1] = {yj}, jz[1] = {zj}, vx[1], vy[1], vz[1];
-                            pair_forces<1>(qx, qy, qz, jx, jy, jz, vx, vy, vz, key);
-                            ax[r] = __dadd_rn(ax[r], vx[0]); ay[r] = __dadd_rn(ay[r], vy[0]); az[r] = __dadd_rn(az[r], vz[0]);
-                            ux = __dsub_rn(ux, vx[0]); uy = __dsub_rn(uy, vy[0]); uz = __dsub_rn(uz, vz[0]);
+                            ax[r] = __dadd_rn(ax[r], vx[u * R + r]);
+                            ay[r] = __dadd_rn(ay[r], vy[u * R + r]);
+                            az[r] = __dadd_rn(az[r], vz[u * R + r]);
+                            ux = __dsub_rn(ux, vx[u * R + r]);
+                            uy = __dsub_rn(uy, vy[u * R + r]);
+                            uz = __dsub_rn(uz, vz[u * R + r]);
                         }
                     }
                 }
-                if (have_u) { rax[e] = ux; ray[e] = uy; raz[e] = uz; }
+                if (have_u) { rax[es[u]] = ux; ray[es[u]] = uy; raz[es[u]] = uz; }
+                __syncwarp();
             }
-            e = (e + 1 == RING) ? 0 : e + 1;
-            __syncwarp();
         };
 
         // U full steps: every lane's source is below the block, no index predicates.  ALLV: the
@@ -247,6 +281,7 @@ nbody_sym_kernel(const double *__restrict__ src, int npad, int n, double *acc, i
                 open_chunk(c);
             }
             const int lim = min(i0, (s / CH + 1) * CH);   // end of the predicate-free run inside this chunk
+            const long long b0 = now();
             if (s >= 31 && s + U <= lim) {
                 if (full) {
 #pragma unroll 1
@@ -255,13 +290,23 @@ nbody_sym_kernel(const double *__restrict__ src, int npad, int n, double *acc, i
 #pragma unroll 1
                     do { fast_group(std::false_type{}); s += U; } while (s + U <= lim);
                 }
+                if (PROF) t_fast += now() - b0;
             } else {
-                slow_step(s);
-                s += 1;
+                edge_group(s);   // may run up to U-1 steps past s_end: every lane is inactive there
+                s += U;
+                if (PROF) t_slow += now() - b0;
             }
         }
         if (last_chunk >= 1) close_chunk(last_chunk - 1);
         close_chunk(last_chunk);   // done[c] = w for the block's own chunks lets worker w+1 in
+        if (PROF) t_work += now() - w_begin;
+    }
+    if (PROF && lane == 0) {
+        unsigned long long *cnt = reinterpret_cast<unsigned long long *>(ctl + 8);
+        atomicAdd(cnt + 0, (unsigned long long)t_wait); atomicAdd(cnt + 1, (unsigned long long)t_open);
+        atomicAdd(cnt + 2, (unsigned long long)t_close); atomicAdd(cnt + 3, (unsigned long long)t_fast);
+        atomicAdd(cnt + 4, (unsigned long long)t_slow); atomicAdd(cnt + 5, (unsigned long long)t_work);
+        atomicAdd(cnt + 6, (unsigned long long)n_chunks);
     }
     if (key >= kRangeLimit) ctl[1] = 1;
 }

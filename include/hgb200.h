@@ -95,6 +95,10 @@ int hgb_nbody_tune(hgb_nbody *h, int block, int unroll, int warps);
 int hgb_nbody_set_symmetric(hgb_nbody *h, int variant, int min_n);
 /* the variant hgb_nbody_step will use on this handle as configured now (0: the standard kernel) */
 int hgb_nbody_symmetric(const hgb_nbody *h);
+/* diagnostics: clock64 spans summed over all warps of the last step run with a profiling variant
+ * (1226, 1423): flag wait, chunk loads, chunk release, predicate-free loop, predicated steps, whole
+ * workers, chunks opened */
+int hgb_nbody_sym_counters(hgb_nbody *h, unsigned long long *out7);
 int hgb_nbody_upload(hgb_nbody *h, const double *pos_aos);       /* all n bodies */
 /* `iterations` steps; *ms (may be NULL) = device time, CUDA events, max over local devices */
 int hgb_nbody_step(hgb_nbody *h, int iterations, float *ms);

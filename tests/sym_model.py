@@ -132,10 +132,12 @@ class SymModel:
                         fast_step(s + u_)
                     self.fast_steps += U
                     s += U
-            else:
-                slow_step(s)
-                self.slow_steps += 1
-                s += 1
+            else:                                   # edge_group: U predicated steps, s stays a multiple of U
+                assert s % U == 0 and (s % CH) + U <= CH
+                for u_ in range(U):
+                    slow_step(s + u_)
+                self.slow_steps += U
+                s += U
         if last_chunk >= 1:
             self.close(w, last_chunk - 1, ring)
         self.close(w, last_chunk, ring)
