@@ -20,7 +20,9 @@ struct NbShard {
     double *mass = nullptr;      // integrator extension: npad masses, zero beyond n
     int *tlist = nullptr;
     int tlist_cap = 0;
-    int *sym_ctl = nullptr;      // pair-symmetric kernel: ticket, range flag, done[] (nbody_sym.cuh)
+    int *sym_ctl = nullptr;      // pair-symmetric kernel: ticket, range flag, profiling counters (nbody_sym.cuh)
+    ulonglong2 *sym_ll = nullptr; // ... tagged chain accumulators, 48 B per body
+    unsigned sym_epoch = 0;
 };
 }  // namespace
 
@@ -87,14 +89,15 @@ constexpr int kSymDefaultMinN = 262144;                    // below this the wav
 
 static bool sym_variant_known(int v) {
     switch (v) {
-        case 124: case 146: case 148: case 224: case 226: case 228: case 243: case 413: case 423: case 422: case 1226: case 1423:
+        case 124: case 146: case 148: case 224: case 226: case 228: case 243: case 413: case 423: case 422: case 242: case 183: case 182: case 144: case 1226: case 1242:
             return true;
     }
     return false;
 }
 
 template <int R, int U, int CTAS, bool PROF = false>
-static int launch_sym_variant(cudaStream_t st, int sms, const double *src, int npad, int n, double *acc, int *ctl) {
+static int launch_sym_variant(cudaStream_t st, int sms, const double *src, int npad, int n, ulonglong2 *ll,
+                              unsigned epoch_tag, int *ctl) {
     const size_t smem = (size_t)kSymWarps * 6 * 3 * 32 * sizeof(double);   // per warp: 6 arrays x 3 chunks of 32
     static bool attr_set = false;   // per instantiation
     if (!attr_set) {
@@ -102,7 +105,7 @@ static int launch_sym_variant(cudaStream_t st, int sms, const double *src, int n
                                       (int)smem));
         attr_set = true;
     }
-    nbody_sym_kernel<R, U, CTAS, PROF><<<sms * CTAS, kSymWarps * 32, smem, st>>>(src, npad, n, acc, ctl);
+    nbody_sym_kernel<R, U, CTAS, PROF><<<sms * CTAS, kSymWarps * 32, smem, st>>>(src, npad, n, ll, epoch_tag, ctl);
     HGB_LAUNCHED();
     return HGB_OK;
 }
@@ -114,27 +117,31 @@ static bool sym_applies(const hgb_nbody *h) {
 // whole step on shard s: tickets/flags reset, wavefront kernel, G*acc, conditional redo
 static int launch_sym(const hgb_nbody *h, NbShard &s, const double *src, const PeerOut &out) {
     cudaStream_t st = s.dev->stream;
-    const int chunks = (h->n + 31) / 32;
-    (void)0;
-    if (!s.sym_ctl) HGB_CUDA(cudaMalloc(&s.sym_ctl, sizeof(int) * (kSymCtlInts + h->npad / 32 + 1)));
+    if (!s.sym_ctl) {
+        HGB_CUDA(cudaMalloc(&s.sym_ctl, sizeof(int) * kSymCtlInts));
+        HGB_CUDA(cudaMalloc(&s.sym_ll, 48ull * h->npad));
+        HGB_CUDA(cudaMemsetAsync(s.sym_ll, 0, 48ull * h->npad, st));   // tag 0 is never expected
+    }
     HGB_CUDA(cudaMemsetAsync(s.sym_ctl, 0, sizeof(int) * kSymCtlInts, st));
-    HGB_CUDA(cudaMemsetAsync(s.sym_ctl + kSymCtlInts, 0xFF, sizeof(int) * chunks, st));   // done[] = -1
+    s.sym_epoch = s.sym_epoch % 2047 + 1;                            // 1..2047: every launch its own tags
+    const unsigned epoch_tag = s.sym_epoch << 21;
+    ulonglong2 *ll = s.sym_ll;
     int sms = 0;
     HGB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s.dev->device));
-    double *acc = s.stage;   // the AoS staging buffer is idle between upload and download
     int rc = HGB_ERR_ARG;
     switch (h->sym) {
-#define HGB_SYM(R_, U_, C_) case R_ * 100 + U_ * 10 + C_: rc = launch_sym_variant<R_, U_, C_>(st, sms, src, h->npad, h->n, acc, s.sym_ctl); break;
+#define HGB_SYM(R_, U_, C_) case R_ * 100 + U_ * 10 + C_: rc = launch_sym_variant<R_, U_, C_>(st, sms, src, h->npad, h->n, ll, epoch_tag, s.sym_ctl); break;
         HGB_SYM(1, 2, 4) HGB_SYM(1, 4, 6) HGB_SYM(1, 4, 8) HGB_SYM(2, 2, 4) HGB_SYM(2, 2, 6) HGB_SYM(2, 2, 8)
-        HGB_SYM(2, 4, 3) HGB_SYM(4, 1, 3) HGB_SYM(4, 2, 3) HGB_SYM(4, 2, 2)
+        HGB_SYM(2, 4, 3) HGB_SYM(4, 1, 3) HGB_SYM(4, 2, 3) HGB_SYM(4, 2, 2) HGB_SYM(2, 4, 2) HGB_SYM(1, 8, 3)
+        HGB_SYM(1, 8, 2) HGB_SYM(1, 4, 4)
 #undef HGB_SYM
         // diagnostic instantiations (clock64 spans -> hgb_nbody_sym_counters): variant + 1000
-        case 1226: rc = launch_sym_variant<2, 2, 6, true>(st, sms, src, h->npad, h->n, acc, s.sym_ctl); break;
-        case 1423: rc = launch_sym_variant<4, 2, 3, true>(st, sms, src, h->npad, h->n, acc, s.sym_ctl); break;
+        case 1226: rc = launch_sym_variant<2, 2, 6, true>(st, sms, src, h->npad, h->n, ll, epoch_tag, s.sym_ctl); break;
+        case 1242: rc = launch_sym_variant<2, 4, 2, true>(st, sms, src, h->npad, h->n, ll, epoch_tag, s.sym_ctl); break;
         default: set_error("no pair-symmetric nbody variant %d", h->sym);
     }
     HGB_TRY(rc);
-    nbody_sym_finish_kernel<<<(h->n + 255) / 256, 256, 0, st>>>(acc, h->npad, h->n, out);
+    nbody_sym_finish_kernel<<<(h->n + 255) / 256, 256, 0, st>>>(ll, h->npad, h->n, out);
     HGB_LAUNCHED();
     // never taken for sane input: an operand left the fast-path range -> ordinary kernel redoes the step
     return launch_step(h, s, src, 0, h->n, nullptr, out, nullptr, s.sym_ctl + 1);
@@ -219,6 +226,7 @@ int hgb_nbody_destroy(hgb_nbody *h) {
         if (s.mass) cudaFree(s.mass);
         if (s.tlist) cudaFree(s.tlist);
         if (s.sym_ctl) cudaFree(s.sym_ctl);
+        if (s.sym_ll) cudaFree(s.sym_ll);
     }
     delete h;
     return HGB_OK;

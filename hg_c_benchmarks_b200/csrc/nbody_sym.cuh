@@ -18,10 +18,10 @@
 //     a per-warp shared-memory ring next to the source position, each lane subtracts its
 //     R pair forces from it in turn (read-modify-write, __syncwarp between steps);
 //   * the ring (three chunks of 32 sources) is fed chunk by chunk from global memory, where the
-//     previous worker left the chain accumulators; `done[chunk] == w-1` (release / acquire) says
-//     worker w-1 is through with the chunk, two chunks (64 steps) after it took it in -- the
-//     minimum distance between consecutive workers, which is what bounds the wavefront's
-//     parallelism (N / (128 * resident warps) must stay well above 1).  Workers take tickets in index order,
+//     previous worker left the chain accumulators as tagged words (payload + tag in one 8-byte
+//     store: no fence, no flag; the loads are issued one chunk ahead and the tags checked when the
+//     chunk is opened).  Worker w publishes a chunk two chunks (64 steps) after it took it in --
+//     the minimum distance between consecutive workers.  Workers take tickets in index order,
 //     so worker w only ever waits for a worker that is already running: no deadlock, and the
 //     grid is persistent (warps loop over tickets);
 //   * the block's own pairs (the diagonal chunks) run through the same skewed schedule with
@@ -40,15 +40,29 @@
 
 namespace hgb {
 
-constexpr int kSymCtlInts = 32;   // ctl[0] = ticket counter, ctl[1] = range flag, done[] follows
+constexpr int kSymCtlInts = 32;   // ctl[0] = ticket counter, ctl[1] = range flag, ctl[8..] profiling counters
 
-__device__ __forceinline__ int sym_ld_acquire(const int *p) {
-    int v;
-    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+// Hand-off words (the "LL" scheme of collective libraries): every 64-bit word carries 32 bits of
+// payload and a 32-bit tag, so a naturally aligned 8-byte store publishes data and flag together --
+// no fence, no separate flag, and the consumer may issue its loads early and look at the tags later.
+// One double = two words; tag = (launch epoch << 21) | (producing worker + 1), never 0.
+__device__ __forceinline__ ulonglong2 ll_load(const ulonglong2 *p) {
+    ulonglong2 v;
+    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p) : "memory");
     return v;
 }
-__device__ __forceinline__ void sym_st_release(int *p, int v) {
-    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+__device__ __forceinline__ void ll_store(ulonglong2 *p, ulonglong2 v) {
+    asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(v.x), "l"(v.y) : "memory");
+}
+__device__ __forceinline__ ulonglong2 ll_pack(double d, unsigned tag) {
+    const unsigned long long b = (unsigned long long)__double_as_longlong(d), t = (unsigned long long)tag << 32;
+    return make_ulonglong2(t | (b & 0xffffffffull), t | (b >> 32));
+}
+__device__ __forceinline__ bool ll_ok(ulonglong2 v, unsigned tag) {
+    return (unsigned)(v.x >> 32) == tag && (unsigned)(v.y >> 32) == tag;
+}
+__device__ __forceinline__ double ll_unpack(ulonglong2 v) {
+    return __longlong_as_double((long long)((v.y << 32) | (v.x & 0xffffffffull)));
 }
 
 // d * f of pair_wise_accel for P independent (target, source) pairs, the dependency chains
@@ -114,12 +128,13 @@ constexpr int kSymWarps = 4;   // warps (independent workers) per CTA
 
 // R targets per lane, U systolic steps per unrolled group (R*U independent pair chains in
 // flight per thread), CTAS resident CTAs per SM (register budget).  src: SoA positions with
-// component stride npad (zero beyond n); acc: SoA chain accumulators, same stride.
+// component stride npad (zero beyond n); ll: tagged chain accumulators, [chunk][x,y,z][32 lanes] x 16 B;
+// epoch_tag: (launch counter mod 2048) << 21, so words of earlier launches never match.
 // PROF: lane 0 of every warp accumulates clock64() spans (flag wait, chunk loads, chunk release, the
 // predicate-free loop, predicated steps, whole workers) into ctl[8..] -- a diagnostic instantiation.
 template <int R, int U, int CTAS, bool PROF = false>
 __global__ void __launch_bounds__(kSymWarps * 32, CTAS)
-nbody_sym_kernel(const double *__restrict__ src, int npad, int n, double *acc, int *ctl) {
+nbody_sym_kernel(const double *__restrict__ src, int npad, int n, ulonglong2 *ll, unsigned epoch_tag, int *ctl) {
     constexpr int BS = 32 * R, CH = 32, RING = 3 * CH;   // block of targets, hand-off chunk, ring entries
     constexpr unsigned FULL = 0xffffffffu;
     static_assert(CH % U == 0, "groups of U steps must not straddle a chunk boundary");
@@ -128,8 +143,6 @@ nbody_sym_kernel(const double *__restrict__ src, int npad, int n, double *acc, i
     double *rx = sym_smem + (threadIdx.x >> 5) * 6 * RING;
     double *ry = rx + RING, *rz = ry + RING, *rax = rz + RING, *ray = rax + RING, *raz = ray + RING;
     const double *sx = src, *sy = src + npad, *sz = src + 2 * (size_t)npad;
-    double *gax = acc, *gay = acc + npad, *gaz = acc + 2 * (size_t)npad;
-    int *done = ctl + kSymCtlInts;
     const int T = (n + BS - 1) / BS;
     unsigned key = 0;
     long long t_wait = 0, t_open = 0, t_close = 0, t_fast = 0, t_slow = 0, t_work = 0, n_chunks = 0;
@@ -152,31 +165,53 @@ nbody_sym_kernel(const double *__restrict__ src, int npad, int n, double *acc, i
         }
         int e = (RING - lane) % RING;   // ring entry of source j = s - lane
 
+        // Prefetch registers: one entry (this lane's) of the chunk that will be opened next -- the
+        // source position and, for a lower chunk, the tagged chain-accumulator words.  The loads are
+        // issued a whole chunk (32 steps) ahead; the tags are only looked at when the chunk is opened.
+        int pf_chunk = -1;
+        double pf_x = 0.0, pf_y = 0.0, pf_z = 0.0;
+        ulonglong2 pf_ax = make_ulonglong2(0, 0), pf_ay = pf_ax, pf_az = pf_ax;
+        const unsigned want_tag = epoch_tag | (unsigned)w;         // written by worker w-1
+        const unsigned my_tag = epoch_tag | (unsigned)(w + 1);
+        auto prefetch_chunk = [&](int c) {
+            const int g = c * CH + lane;
+            pf_x = sx[g]; pf_y = sy[g]; pf_z = sz[g];
+            if (c < w * R) {
+                const ulonglong2 *q = ll + (size_t)c * 3 * CH + lane;
+                pf_ax = ll_load(q); pf_ay = ll_load(q + CH); pf_az = ll_load(q + 2 * CH);
+            }
+            pf_chunk = c;
+        };
         // chunk c (32 sources) enters the ring: positions always, chain accumulators once worker w-1
-        // released them (chunks of the block itself get theirs from the owning lanes)
+        // has published them (chunks of the block itself get theirs from the owning lanes)
         auto open_chunk = [&](int c) {
-            const int slot = (c % 3) * CH + lane, g = c * CH + lane;
+            const int slot = (c % 3) * CH + lane;
             const bool lower = c < w * R;
             const long long a0 = now();
-            if (lower)
-                while (sym_ld_acquire(done + c) != w - 1) __nanosleep(32);
-            const long long a1 = now();
-            rx[slot] = sx[g]; ry[slot] = sy[g]; rz[slot] = sz[g];
+            if (pf_chunk != c) prefetch_chunk(c);
             if (lower) {
-                rax[slot] = __ldcg(gax + g); ray[slot] = __ldcg(gay + g); raz[slot] = __ldcg(gaz + g);
+                const ulonglong2 *q = ll + (size_t)c * 3 * CH + lane;
+                // every lane polls its own three entries; the warp leaves together
+                while (!__all_sync(FULL, ll_ok(pf_ax, want_tag) && ll_ok(pf_ay, want_tag) && ll_ok(pf_az, want_tag))) {
+                    __nanosleep(20);
+                    pf_ax = ll_load(q); pf_ay = ll_load(q + CH); pf_az = ll_load(q + 2 * CH);
+                }
             }
+            const long long a1 = now();
+            rx[slot] = pf_x; ry[slot] = pf_y; rz[slot] = pf_z;
+            if (lower) { rax[slot] = ll_unpack(pf_ax); ray[slot] = ll_unpack(pf_ay); raz[slot] = ll_unpack(pf_az); }
             __syncwarp();
             if (PROF) { t_wait += a1 - a0; t_open += now() - a1; ++n_chunks; }
         };
-        // every lane is through with chunk c: hand its chain accumulators to worker w+1.  The warp
-        // barrier orders the lanes' stores before lane 0's release (cumulative), as in a grid barrier.
+        // every lane is through with chunk c: publish its chain accumulators for worker w+1
         auto close_chunk = [&](int c) {
-            const int slot = (c % 3) * CH + lane, g = c * CH + lane;
+            const int slot = (c % 3) * CH + lane;
             const long long a0 = now();
             __syncwarp();
-            gax[g] = rax[slot]; gay[g] = ray[slot]; gaz[g] = raz[slot];
-            __syncwarp();
-            if (lane == 0) sym_st_release(done + c, w);
+            ulonglong2 *q = ll + (size_t)c * 3 * CH + lane;
+            ll_store(q, ll_pack(rax[slot], my_tag));
+            ll_store(q + CH, ll_pack(ray[slot], my_tag));
+            ll_store(q + 2 * CH, ll_pack(raz[slot], my_tag));
             if (PROF) { __syncwarp(); t_close += now() - a0; }
         };
         // U predicated steps starting at step s0 (a multiple of U, so the group stays inside one chunk):
@@ -279,6 +314,7 @@ nbody_sym_kernel(const double *__restrict__ src, int npad, int n, double *acc, i
                 const int c = s / CH;
                 if (c >= 2) close_chunk(c - 2);   // lane 31 left it 2 steps ago at the latest
                 open_chunk(c);
+                if (c + 1 <= last_chunk) prefetch_chunk(c + 1);
             }
             const int lim = min(i0, (s / CH + 1) * CH);   // end of the predicate-free run inside this chunk
             const long long b0 = now();
@@ -298,7 +334,7 @@ nbody_sym_kernel(const double *__restrict__ src, int npad, int n, double *acc, i
             }
         }
         if (last_chunk >= 1) close_chunk(last_chunk - 1);
-        close_chunk(last_chunk);   // done[c] = w for the block's own chunks lets worker w+1 in
+        close_chunk(last_chunk);   // the block's own chunks, tagged w+1, let worker w+1 in
         if (PROF) t_work += now() - w_begin;
     }
     if (PROF && lane == 0) {
@@ -311,12 +347,13 @@ nbody_sym_kernel(const double *__restrict__ src, int npad, int n, double *acc, i
     if (key >= kRangeLimit) ctl[1] = 1;
 }
 
-// buffer[i] = G * acc[i] (reference src/nbody/nbody-run.c:22-24)
-__global__ void nbody_sym_finish_kernel(const double *__restrict__ acc, int npad, int n, PeerOut out) {
+// buffer[i] = G * acc[i] (reference src/nbody/nbody-run.c:22-24); acc = what the last worker published
+__global__ void nbody_sym_finish_kernel(const ulonglong2 *__restrict__ ll, int npad, int n, PeerOut out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const double gx = __dmul_rn(kG, acc[i]), gy = __dmul_rn(kG, acc[(size_t)npad + i]),
-                 gz = __dmul_rn(kG, acc[2 * (size_t)npad + i]);
+    const ulonglong2 *q = ll + (size_t)(i / 32) * 3 * 32 + (i % 32);
+    const double gx = __dmul_rn(kG, ll_unpack(q[0])), gy = __dmul_rn(kG, ll_unpack(q[32])),
+                 gz = __dmul_rn(kG, ll_unpack(q[64]));
     for (int p = 0; p < out.count; ++p) {
         double *o = out.base[p];
         o[i] = gx; o[(size_t)npad + i] = gy; o[2 * (size_t)npad + i] = gz;

@@ -18,7 +18,7 @@ pytestmark = [pytest.mark.gpu]
 if os.environ.get("HGB_TEST_SYM", "0") == "0":      # opt-in until the kernel has its first green GPU run
     pytestmark.append(pytest.mark.skip(reason="HGB_TEST_SYM not set"))
 
-VARIANTS = (124, 146, 148, 224, 226, 228, 243, 413, 422, 423)   # R*100 + U*10 + CTAs per SM
+VARIANTS = (124, 144, 146, 148, 182, 183, 224, 226, 228, 242, 243, 413, 422, 423)   # R*100 + U*10 + CTAs per SM
 
 
 def sha(a):

@@ -11,7 +11,7 @@ from hg_c_benchmarks_b200 import synth  # noqa: E402
 NAMES = ("flag wait", "chunk loads", "chunk release", "fast loop", "predicated steps", "workers total", "chunks")
 for n in [int(a) for a in sys.argv[1:]] or [65536, 1 << 20]:
     pos = synth.uniform_cube(n, seed=1)
-    for v in (1226, 1423):
+    for v in (1226, 1242):
         with H.nbody.NBody(n) as nb:
             nb.symmetric(v, 0).upload(pos)
             nb.step(1)
