@@ -84,12 +84,12 @@ static int launch_step(const hgb_nbody *h, const NbShard &s, const double *src, 
 
 // ---- pair-symmetric step (nbody_sym.cuh): one GPU, EXACT mode, all n targets --------------
 static int g_default_sym = -1, g_default_sym_min_n = -1;   // -1: read HGB_NBODY_SYM / HGB_NBODY_SYM_MIN_N
-constexpr int kSymDefaultVariant = 423;                    // R = 4, U = 2, 3 CTAs (12 warps) per SM
-constexpr int kSymDefaultMinN = 262144;                    // below this the wavefront ramp dominates
+constexpr int kSymDefaultVariant = 242;                    // R = 2, U = 4, 2 CTAs (8 warps) per SM: profiles/r1e_nbody_sym_sweep_*.txt
+constexpr int kSymDefaultMinN = 393216;                    // measured: slower than the standard kernel at 2^18, 26 % faster at 2^19
 
 static bool sym_variant_known(int v) {
     switch (v) {
-        case 124: case 146: case 148: case 224: case 226: case 228: case 243: case 413: case 423: case 422: case 242: case 183: case 182: case 144: case 1226: case 1242:
+        case 124: case 146: case 148: case 224: case 226: case 228: case 243: case 413: case 423: case 422: case 242: case 183: case 182: case 144: case 241: case 181: case 421: case 1226: case 1242:
             return true;
     }
     return false;
@@ -133,7 +133,7 @@ static int launch_sym(const hgb_nbody *h, NbShard &s, const double *src, const P
 #define HGB_SYM(R_, U_, C_) case R_ * 100 + U_ * 10 + C_: rc = launch_sym_variant<R_, U_, C_>(st, sms, src, h->npad, h->n, ll, epoch_tag, s.sym_ctl); break;
         HGB_SYM(1, 2, 4) HGB_SYM(1, 4, 6) HGB_SYM(1, 4, 8) HGB_SYM(2, 2, 4) HGB_SYM(2, 2, 6) HGB_SYM(2, 2, 8)
         HGB_SYM(2, 4, 3) HGB_SYM(4, 1, 3) HGB_SYM(4, 2, 3) HGB_SYM(4, 2, 2) HGB_SYM(2, 4, 2) HGB_SYM(1, 8, 3)
-        HGB_SYM(1, 8, 2) HGB_SYM(1, 4, 4)
+        HGB_SYM(1, 8, 2) HGB_SYM(1, 4, 4) HGB_SYM(2, 4, 1) HGB_SYM(1, 8, 1) HGB_SYM(4, 2, 1)
 #undef HGB_SYM
         // diagnostic instantiations (clock64 spans -> hgb_nbody_sym_counters): variant + 1000
         case 1226: rc = launch_sym_variant<2, 2, 6, true>(st, sms, src, h->npad, h->n, ll, epoch_tag, s.sym_ctl); break;
@@ -163,8 +163,8 @@ static int nb_alloc(hgb_nbody *h) {
 
 static void sym_defaults(hgb_nbody *h) {
     if (g_default_sym < 0) {
-        const char *e = getenv("HGB_NBODY_SYM");
-        int v = e ? atoi(e) : 0;
+        const char *e = getenv("HGB_NBODY_SYM");   // unset: on (default variant); 0: off; else a variant
+        int v = e ? atoi(e) : 1;
         if (v == 1) v = kSymDefaultVariant;
         g_default_sym = sym_variant_known(v) ? v : 0;
     }
@@ -312,6 +312,7 @@ int hgb_nbody_tune(hgb_nbody *h, int block, int unroll, int warps) {
     h->block = block;
     h->unroll = unroll;
     h->warps = warps;
+    if (block || unroll || warps) h->sym = 0;   // an explicit variant of the standard kernel was asked for
     return HGB_OK;
 }
 

@@ -91,12 +91,13 @@ int hgb_nbody_tune(hgb_nbody *h, int block, int unroll, int warps);
  * 17-25), so the result is bit-identical to hgb_nbody_tune's kernel at 16 instead of 29 FP64
  * instructions per interaction.  variant: 0 = off, 1 = default, else R*100 + U*10 + CTAs per SM;
  * used on single-GPU handles in EXACT mode when n >= min_n (the wavefront needs a large n to fill
- * the GPU).  New handles take their default from env HGB_NBODY_SYM / HGB_NBODY_SYM_MIN_N. */
+ * the GPU).  New handles default to variant 1 with min_n = 393216 (env HGB_NBODY_SYM = 0 | 1 | variant
+ * and HGB_NBODY_SYM_MIN_N override); hgb_nbody_tune with a non-zero argument switches it off. */
 int hgb_nbody_set_symmetric(hgb_nbody *h, int variant, int min_n);
 /* the variant hgb_nbody_step will use on this handle as configured now (0: the standard kernel) */
 int hgb_nbody_symmetric(const hgb_nbody *h);
 /* diagnostics: clock64 spans summed over all warps of the last step run with a profiling variant
- * (1226, 1423): flag wait, chunk loads, chunk release, predicate-free loop, predicated steps, whole
+ * (1226, 1242): tag wait, chunk loads, chunk release, predicate-free loop, predicated steps, whole
  * workers, chunks opened */
 int hgb_nbody_sym_counters(hgb_nbody *h, unsigned long long *out7);
 int hgb_nbody_upload(hgb_nbody *h, const double *pos_aos);       /* all n bodies */
