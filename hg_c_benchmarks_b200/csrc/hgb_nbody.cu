@@ -277,6 +277,7 @@ int hgb_nbody_create_rank(hgb_nbody **out, int n) {
     h->npad = h->slice * r.world;
     h->mode = g_default_mode;
     h->exchange = HGB_EXCHANGE_NCCL;
+    sym_defaults(h);                 // applies when the communicator has a single rank
     h->sh.resize(1);
     h->sh[0].dev = &r.rank_dev;
     h->sh[0].index = r.rank;
