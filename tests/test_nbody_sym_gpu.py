@@ -159,3 +159,36 @@ def test_sym_is_ignored_where_it_does_not_apply(hgb):
         assert np.array_equal(nb.download(), want)
     with pytest.raises(hgb.HgbError):
         hgb.nbody.NBody(n).symmetric(999, 0)
+
+
+def test_sym_default_policy(hgb):
+    """new one-GPU handles use the symmetric kernel from n = 393216 up; an explicit hgb_nbody_tune
+    variant of the standard kernel, FAST mode or a small n switch it off"""
+    L = hgb.lib()
+    if os.environ.get("HGB_NBODY_SYM") or os.environ.get("HGB_NBODY_SYM_MIN_N"):
+        pytest.skip("defaults overridden by the environment")
+    with hgb.nbody.NBody(393216) as nb:
+        assert L.hgb_nbody_symmetric(nb._h) == 242
+        nb.tune(128, 2, 24)
+        assert L.hgb_nbody_symmetric(nb._h) == 0
+    with hgb.nbody.NBody(393215) as nb:
+        assert L.hgb_nbody_symmetric(nb._h) == 0
+        nb.symmetric(1, 0)
+        assert L.hgb_nbody_symmetric(nb._h) == 242
+    with hgb.nbody.NBody(1 << 19, mode=hgb.NBODY_FAST) as nb:
+        assert L.hgb_nbody_symmetric(nb._h) == 0
+
+
+def test_sym_many_steps_reuse_the_tagged_buffer(hgb):
+    """epoch tags: 40 consecutive launches on one handle (and an upload in between) never see stale words"""
+    from oracle import port
+    n = 700
+    pos = synth.uniform_cube(n, seed=21)
+    a, b = pos.copy(), np.zeros_like(pos)
+    port.nbody_run(a, b, 4)
+    with hgb.nbody.NBody(n) as nb:
+        nb.symmetric(1, 0).upload(pos)
+        nb.step(37)
+        nb.upload(pos)
+        nb.step(4)
+        assert np.array_equal(nb.download(), a)
