@@ -192,3 +192,20 @@ def test_sym_many_steps_reuse_the_tagged_buffer(hgb):
         nb.upload(pos)
         nb.step(4)
         assert np.array_equal(nb.download(), a)
+
+
+def test_sym_epoch_counter_wraps_cleanly(hgb):
+    """the launch epoch in the tags is 11 bits (1..2047): results stay exact across the wrap"""
+    from oracle import port
+    n = 100
+    pos = synth.uniform_cube(n, seed=33)
+    want = np.zeros_like(pos)
+    port.nbody_step_range(pos, want, 0, n)
+    with hgb.nbody.NBody(n) as nb:
+        nb.symmetric(1, 0)
+        for it in range(2100):
+            nb.upload(pos)
+            nb.step(1)
+            if it % 300 == 0 or 2040 <= it <= 2052:
+                assert np.array_equal(nb.download(), want), it
+        assert np.array_equal(nb.download(), want)
