@@ -296,6 +296,19 @@ def main():
     e2e_ms = max_over_ranks(sum(e2e_ms) / len(e2e_ms))
     nb.close()
 
+    # like-for-like scaling base: when N=1 runs the pair-symmetric kernel, also time the standard
+    # (one target per thread) kernel that the multi-GPU runs use, same inputs, 1 warm-up + 1 step
+    standard = None
+    if sym and world == 1:
+        with H.nbody.NBody(n, ngpus=None, mode=H.NBODY_EXACT) as nb_std:
+            nb_std.symmetric(0, 0).upload(pos_np)
+            nb_std.step(1)
+            H._abi.check(L.hgb_flush_l2())
+            std_ms = nb_std.step(1)
+        standard = {"kernel": "nbody_step_kernel<128,2,24,false>", "value": float(n) * n / (std_ms * 1e-3),
+                    "unit": "interactions/s", "ms_per_step": std_ms, "steps": 1,
+                    "note": "the kernel every rank runs at N > 1 (targets sharded); scaling of that kernel is value(N) / this"}
+
     # ---------------- convolution 16384^2, 3x3 and 7x7 ----------------------------------------
     conv = {}
     if not args.skip_conv:
@@ -382,6 +395,8 @@ def main():
                          "probe_sm_mhz": mhz.value, "hbm_copy_probe_gbs": gbs.value},
             "conv": conv,
         }
+        if standard:
+            line["nbody_standard_kernel"] = standard
         if world == 1 and not args.skip_cpu:
             line["cpu_baseline"] = cpu_baseline()
         print(json.dumps(line), file=OUT, flush=True)
