@@ -98,13 +98,7 @@ static bool sym_variant_known(int v) {
 template <int R, int U, int CTAS, bool PROF = false>
 static int launch_sym_variant(cudaStream_t st, int sms, const double *src, int npad, int n, ulonglong2 *ll,
                               unsigned epoch_tag, int *ctl) {
-    const size_t smem = (size_t)kSymWarps * 6 * 3 * 32 * sizeof(double);   // per warp: 6 arrays x 3 chunks of 32
-    static bool attr_set = false;   // per instantiation
-    if (!attr_set) {
-        HGB_CUDA(cudaFuncSetAttribute(nbody_sym_kernel<R, U, CTAS, PROF>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)smem));
-        attr_set = true;
-    }
+    const size_t smem = (size_t)kSymWarps * 6 * 3 * 32 * sizeof(double);   // per warp: 6 arrays x 3 chunks of 32 (18 KB per CTA)
     nbody_sym_kernel<R, U, CTAS, PROF><<<sms * CTAS, kSymWarps * 32, smem, st>>>(src, npad, n, ll, epoch_tag, ctl);
     HGB_LAUNCHED();
     return HGB_OK;
