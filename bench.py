@@ -35,6 +35,12 @@ FP64_INSTR_PER_INTERACTION_SYM = 16  # pair-symmetric kernel: 26 + 3 + 3 FP64-pi
 BYTES_PER_PIXEL = 16               # 8 B read + 8 B written per inner pixel per iteration
 
 
+def workload(n):
+    """config.workload, shared by both arms (the reference arm runs a bounded sample of it)"""
+    return (f"nbody N={n} uniform cube seed 1, all-pairs FP64, EXACT mode (bit-identical to the reference), "
+            "BASELINE configs[3]")
+
+
 def env_rank():
     return (int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0")),
             int(os.environ.get("WORLD_SIZE", "1")))
@@ -149,7 +155,8 @@ def run_reference(args):
             "unit": "interactions/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"nbody N={N_BODIES} uniform cube seed 1 (CPU: bounded sample, see cpu_baseline.sample)"},
+            "config": {"workload": workload(N_BODIES),
+                       "sample": "CPU arm: a bounded sample of the workload per step, see cpu_baseline.sample"},
             "cpu_baseline": {"value": value, "unit": "interactions/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": "interactions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -371,7 +378,7 @@ def main():
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": {"workload": f"nbody N={n} uniform cube seed 1, all-pairs FP64, EXACT mode (bit-identical to the reference), BASELINE configs[3]",
+            "config": {"workload": workload(n),
                        "kernel": nb_kernel,
                        "parallelism": f"targets sharded over {world} GPU(s), ncclAllGather of positions per step",
                        "l2": "512 MiB fill between timed steps (nbody); convolution inputs (2 GiB) exceed L2",
