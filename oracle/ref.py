@@ -13,39 +13,47 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _REF = os.path.join(_HERE, "_ref")
 _dp = C.POINTER(C.c_double)
-_NB = None
-_CV = None
+_NB = {}
+_CV = {}
+# "" = the shipped effective flags (nbody -O2, convolution -O3); "_pgo" = the same sources at
+# -O3 with gcc profile feedback, i.e. what the reference's pgo.sh intended (oracle/Makefile)
+_VARIANT = ""
 
 
-def build(reference="/root/reference"):
+def build(reference="/root/reference", pgo=True):
     if not os.path.isdir(reference):
         raise RuntimeError("reference sources not present; oracle/_ref cannot be (re)built here")
-    subprocess.run(["make", "-C", _HERE, "ref", f"REF={reference}"], check=True,
-                   capture_output=True)
+    subprocess.run(["make", "-C", _HERE, "ref"] + (["ref-pgo"] if pgo else []) + [f"REF={reference}"],
+                   check=True, capture_output=True)
 
 
-def available():
-    return (os.path.exists(os.path.join(_REF, "libhgref_nbody.so"))
-            and os.path.exists(os.path.join(_REF, "libhgref_conv.so")))
+def available(variant=""):
+    return (os.path.exists(os.path.join(_REF, f"libhgref_nbody{variant}.so"))
+            and os.path.exists(os.path.join(_REF, f"libhgref_conv{variant}.so")))
+
+
+def use(variant=""):
+    """select which build of the unmodified reference the functions below call: "" or "_pgo" """
+    global _VARIANT
+    assert variant in ("", "_pgo") and available(variant), variant
+    _VARIANT = variant
 
 
 def _nb():
-    global _NB
-    if _NB is None:
-        L = C.CDLL(os.path.join(_REF, "libhgref_nbody.so"))
+    if _VARIANT not in _NB:
+        L = C.CDLL(os.path.join(_REF, f"libhgref_nbody{_VARIANT}.so"))
         # void run(Float3D*, Float3D*, int, int, int)   src/nbody/nbody-run.h:46
         L.run.argtypes = [_dp, _dp, C.c_int, C.c_int, C.c_int]
         L.run.restype = None
         L.fill_planet.argtypes = [_dp, C.c_int]  # src/nbody/nbody-util.h:54
         L.fill_planet.restype = None
-        _NB = L
-    return _NB
+        _NB[_VARIANT] = L
+    return _NB[_VARIANT]
 
 
 def _cv():
-    global _CV
-    if _CV is None:
-        L = C.CDLL(os.path.join(_REF, "libhgref_conv.so"))
+    if _VARIANT not in _CV:
+        L = C.CDLL(os.path.join(_REF, f"libhgref_conv{_VARIANT}.so"))
         L.ref_conv_run_flat.argtypes = [_dp, _dp, C.c_int, C.c_int, C.c_int, _dp, C.c_int, C.c_int,
                                         C.c_int, C.c_int]
         L.ref_add_padding_flat.argtypes = [_dp, _dp, C.c_int, C.c_int, C.c_int]
@@ -54,8 +62,8 @@ def _cv():
         L.ref_read_image.argtypes = [C.c_char_p, _dp, C.c_int, C.POINTER(C.c_int),
                                      C.POINTER(C.c_int)]
         L.ref_default_kernel.argtypes = [_dp]
-        _CV = L
-    return _CV
+        _CV[_VARIANT] = L
+    return _CV[_VARIANT]
 
 
 def _p(a):

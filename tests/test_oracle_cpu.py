@@ -227,6 +227,32 @@ def test_conv_port_equals_reference_binary():
         assert port.conv_checksum(a, w, h, p) == ref.conv_checksum(c, w, h, p)
 
 
+@pytest.mark.skipif(not (ref.available() and ref.available("_pgo")),
+                    reason="oracle/_ref PGO build not present (make -C oracle ref-pgo)")
+def test_pgo_build_of_the_reference_is_bit_identical_to_the_shipped_flags():
+    """the -O3 + profile-feedback build (what pgo.sh intended) is a second CPU baseline for
+    bench.py; it must compute exactly what the shipped-flags build computes"""
+    try:
+        res = {}
+        for v in ("", "_pgo"):
+            ref.use(v)
+            out = []
+            for pos, iters, procs in ((synth.fill_planets(9), 4, 1), (synth.plummer(1500), 3, 4)):
+                a, b = pos.copy(), np.zeros_like(pos)
+                ref.nbody_run(a, b, iters, procs)
+                out += [a, b]
+            for (w, h, k, it) in [(130, 70, 3, 3), (64, 48, 5, 2), (97, 33, 7, 2)]:
+                p = k // 2
+                c, d = ref.add_padding(synth.image_float(w, h, seed=k), p), np.zeros((h, w + 2 * p))
+                ref.conv_run(c, d, w, h, p, synth.kernel_dense(k), it, 3)
+                out += [c, d, np.array([ref.conv_checksum(c, w, h, p)])]
+            res[v] = out
+        for x, y in zip(res[""], res["_pgo"]):
+            assert np.array_equal(x.view(np.uint64), y.view(np.uint64))
+    finally:
+        ref.use("")
+
+
 @pytest.mark.skipif(not os.path.isdir("/root/reference"), reason="reference tree not present")
 def test_golden_fixture_is_the_shipped_file(shipped_image):
     img = ref.read_image("/root/reference/2d-convolution.input")
