@@ -51,6 +51,46 @@ def conv_halo_plan(h, p, world, rank):
     return plan
 
 
+CONV_HALO_ROWS = 32   # csrc/hgb_conv.cu kBnd: halo capacity per side of a band
+
+
+def conv_eff_depth(h, p, world, depth=0, fused3x3=False):
+    """iterations per halo exchange (csrc/hgb_conv.cu eff_depth): the request (0 = automatic: 8, or
+    16 where 3x3 passes run two iterations each) clamped by the halo capacity and the shortest band"""
+    act = conv_active_ranks(h, p, world)
+    if act <= 1 or p <= 0:
+        return 1
+    halo = CONV_HALO_ROWS if p < CONV_HALO_ROWS else p
+    d = depth if depth > 0 else (16 if (p == 1 and fused3x3) else 8)
+    d = min(d, halo // p, (h // act) // p)
+    return max(1, d)
+
+
+def conv_cycle_rows(h, p, world, rank, d, t):
+    """global rows [lo, hi) that `rank` computes in iteration t of a cycle of d iterations: its
+    band plus the shrinking fringe of (d-1-t)*p rows per side (communication-avoiding halo)"""
+    r0, rows = conv_band(h, p, world, rank)
+    if rows == 0:
+        return h, h
+    ext = (d - 1 - t) * p
+    return max(0, r0 - ext), min(h, r0 + rows + ext)
+
+
+def conv_deep_halo_plan(h, p, world, rank, d):
+    """one exchange of d*p rows per side after a cycle: (peer, send(lo,hi), recv(lo,hi)), global rows"""
+    act = conv_active_ranks(h, p, world)
+    r0, rows = conv_band(h, p, world, rank)
+    xr = d * p
+    plan = []
+    if rows == 0 or p == 0:
+        return plan
+    if rank > 0:
+        plan.append((rank - 1, (r0, r0 + xr), (r0 - xr, r0)))
+    if rank < act - 1:
+        plan.append((rank + 1, (r0 + rows - xr, r0 + rows), (r0 + rows, r0 + rows + xr)))
+    return plan
+
+
 def env_rank():
     return (int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0")),
             int(os.environ.get("WORLD_SIZE", "1")))

@@ -122,6 +122,83 @@ def test_conv_row_bands_with_halo_exchange_gloo(world, w, h, k, iters):
     assert np.array_equal(got, want)
 
 
+def _conv_deep_rank(rank, world, port_no, w, h, p, k, iters, depth, q):
+    """the communication-avoiding schedule of csrc/hgb_conv.cu hgb_conv_step on CPU: depth*p halo rows
+    travel once per cycle of `depth` iterations, the shrinking fringe is recomputed in between"""
+    from oracle import port
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port_no}", rank=rank, world_size=world)
+    kern = synth.kernel_dense(k)
+    full = synth.add_padding(synth.image_float(w, h, seed=5), p)
+    r0, rows = plan.conv_band(h, p, world, rank)
+    d_eff = plan.conv_eff_depth(h, p, world, depth)
+    xr = d_eff * p
+    cur = np.full_like(full, np.nan)          # rows outside band + halo are poison
+    if rows:
+        cur[max(0, r0 - xr):min(h, r0 + rows + xr)] = full[max(0, r0 - xr):min(h, r0 + rows + xr)]
+    exchanges = 0
+    it = 0
+    while it < iters:
+        d = min(d_eff, iters - it)
+        for t in range(d):
+            nxt = np.full_like(full, np.nan)
+            lo, hi = plan.conv_cycle_rows(h, p, world, rank, d, t)
+            if rows:
+                port.conv_step_rows(cur, nxt, w, h, p, kern, lo, hi, threads=1)
+            cur = nxt
+            it += 1
+        reqs, bufs = [], []
+        for peer, (s0, s1), (v0, v1) in plan.conv_deep_halo_plan(h, p, world, rank, d_eff):
+            reqs.append(dist.isend(torch.from_numpy(cur[s0:s1].copy()), peer))
+            tbuf = torch.empty((v1 - v0, w + 2 * p), dtype=torch.float64)
+            bufs.append((v0, v1, tbuf))
+            reqs.append(dist.irecv(tbuf, peer))
+        for r in reqs:
+            r.wait()
+        for v0, v1, tbuf in bufs:
+            cur[v0:v1] = tbuf.numpy()
+        exchanges += 1
+    q.put((rank, r0, rows, cur[r0:r0 + rows].copy(), exchanges, d_eff))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,w,h,k,iters,depth", [(2, 40, 31, 3, 7, 3), (2, 33, 40, 7, 5, 2), (3, 25, 30, 5, 6, 0),
+                                                     (2, 24, 9, 3, 5, 8), (2, 16, 6, 7, 3, 4)])
+def test_conv_deep_halo_schedule_gloo(world, w, h, k, iters, depth):
+    from oracle import port
+    p = k // 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port_no = _free_port()
+    procs = [ctx.Process(target=_conv_deep_rank, args=(r, world, port_no, w, h, p, k, iters, depth, q))
+             for r in range(world)]
+    for pr in procs:
+        pr.start()
+    parts = [q.get(timeout=300) for _ in range(world)]
+    for pr in procs:
+        pr.join(timeout=120)
+        assert pr.exitcode == 0
+    want = synth.add_padding(synth.image_float(w, h, seed=5), p)
+    prev = np.zeros_like(want)
+    port.conv_run(want, prev, w, h, p, synth.kernel_dense(k), iters)
+    got = np.full_like(want, np.nan)
+    for _, r0, rows, band, exchanges, d_eff in parts:
+        got[r0:r0 + rows] = band
+        assert exchanges == -(-iters // d_eff)            # one exchange per cycle, not per iteration
+        assert 1 <= d_eff <= max(1, (h // plan.conv_active_ranks(h, p, world)) // p)
+    assert np.array_equal(got, want)
+
+
+def test_conv_eff_depth_clamps():
+    assert plan.conv_eff_depth(16384, 1, 8) == 8                    # automatic
+    assert plan.conv_eff_depth(16384, 1, 8, fused3x3=True) == 16    # 3x3 with two iterations per pass
+    assert plan.conv_eff_depth(16384, 3, 8) == 8
+    assert plan.conv_eff_depth(16384, 3, 8, depth=20) == 10         # halo capacity: 32 rows / p
+    assert plan.conv_eff_depth(40, 1, 8, depth=16) == 5             # shortest band: 5 rows
+    assert plan.conv_eff_depth(16384, 1, 1, depth=16) == 1          # one band: nothing to exchange
+    assert plan.conv_eff_depth(6, 3, 2, depth=4) == 1
+
+
 def test_plans_cover_everything_once():
     for n in (1, 3, 1000, 1024, 1025, 65536, 1 << 20):
         for world in (1, 2, 3, 4, 8):
