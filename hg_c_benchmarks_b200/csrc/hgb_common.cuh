@@ -8,6 +8,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <deque>
+#include <map>
 #include <string>
 #include <vector>
 
@@ -82,17 +84,21 @@ int nccl_load();  // HGB_OK or HGB_ERR_NCCL
 // ---- devices -------------------------------------------------------------
 struct DevCtx {
     int device = -1;
+    int sms = 0;                    // multiprocessor count of `device`
     cudaStream_t stream = nullptr;  // all kernels + collectives of this device
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr, ev_step = nullptr;
     cudaStream_t stream2 = nullptr; // boundary rows + halo exchange, overlapped with the interior
     cudaEvent_t ev_bnd[2] = {nullptr, nullptr}, ev_int[2] = {nullptr, nullptr}, ev_join = nullptr;
-    ncclComm_t comm = nullptr;      // single-process communicator (ncclCommInitAll)
     void *flush_buf = nullptr;      // L2 flush scratch
 };
 
 struct Runtime {
-    std::vector<DevCtx> devs;       // single-process mode: devices 0..g-1
-    int comm_devs = 0;              // how many of devs share an InitAll communicator
+    // single-process mode: devices 0..g-1.  A deque: handles keep DevCtx* into it, and growing it
+    // for a handle with more GPUs must not move the contexts older handles point at.
+    std::deque<DevCtx> devs;
+    // ncclCommInitAll communicator sets, one per GPU count in use (a g=2 handle and a g=4 handle can
+    // alternate without tearing communicators down)
+    std::map<int, std::vector<ncclComm_t>> sp_comms;
     bool peer_enabled = false;
     // one-process-per-GPU mode
     ncclComm_t rank_comm = nullptr;
@@ -107,7 +113,8 @@ int device_count_checked(int *count);       // HGB_ERR_NOGPU when there is none
 int resolve_ngpus(int requested, int *out); // clamp + HGB_NGPUS override
 bool oversubscribed(int g);                 // g shards on fewer devices (HGB_VIRTUAL_GPUS)
 int ensure_devices(int g);                  // streams/events for devices 0..g-1
-int ensure_sp_comm(int g);                  // ncclCommInitAll over devices 0..g-1
+int ensure_sp_comm(int g);                  // ncclCommInitAll over devices 0..g-1 (cached per g)
+ncclComm_t sp_comm(int g, int index);       // communicator of device `index` in the set of g (after ensure_sp_comm)
 int ensure_peer_access(int g);
 int ensure_rank_dev();                      // stream/events on the current device
 int init_dev(DevCtx &d, int device);

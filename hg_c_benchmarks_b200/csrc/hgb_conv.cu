@@ -213,7 +213,7 @@ static int halo_exchange(hgb_conv *h, int b, bool side = false) {
     HGB_NCCL(nccl().GroupStart());
     for (CvShard &s : h->sh) {
         if (s.rows <= 0) continue;
-        ncclComm_t comm = h->rank_mode ? rt().rank_comm : s.dev->comm;
+        ncclComm_t comm = h->rank_mode ? rt().rank_comm : sp_comm(h->world, s.index);
         double *base = s.img[b];
         if (s.index > 0) {
             HGB_NCCL(nccl().Send(base + (size_t)h->halo * h->dp, cnt, ncclDouble, s.index - 1, comm,

@@ -137,7 +137,25 @@ int hgb_image_read_binary(const char *path, int *width, int *height, double **da
         set_error("%s is not an HGBIMG1 file", path);
         return HGB_ERR_ARG;
     }
+    // same extent clamp as the text reader; and the payload must really be in the file before
+    // anything is allocated for it (a crafted header must not size the buffer)
+    if (hw[0] > (1 << 20) || hw[1] > (1 << 20)) {
+        fclose(f);
+        set_error("%s: image extent %d x %d out of range", path, hw[0], hw[1]);
+        return HGB_ERR_ARG;
+    }
     const size_t count = (size_t)hw[0] * (size_t)hw[1];
+    {
+        const long here = ftell(f);
+        long end = -1;
+        if (here >= 0 && fseek(f, 0, SEEK_END) == 0) end = ftell(f);
+        if (here < 0 || end < 0 || fseek(f, here, SEEK_SET) != 0 ||
+            (unsigned long long)(end - here) < (unsigned long long)count * sizeof(double)) {
+            fclose(f);
+            set_error("%s is truncated", path);
+            return HGB_ERR_ARG;
+        }
+    }
     double *img = static_cast<double *>(malloc(count * sizeof(double)));
     if (!img) { fclose(f); set_error("out of host memory"); return HGB_ERR_ARG; }
     if (fread(img, 8, count, f) != count) {

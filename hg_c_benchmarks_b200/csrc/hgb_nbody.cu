@@ -56,14 +56,30 @@ static void launch_variant(bool fast, int grid, cudaStream_t st, const double *s
                                                                              tlist, out, out_list, none, run_if);
 }
 
+// CTA shape for `count` targets when the caller did not pin one (hgb_nbody_tune).  Large counts:
+// 128-thread CTAs, 6 per SM (measured best at N = 2^20, profiles/r1_nbody_sweep.txt).  When the grid is
+// below one wave the step lasts as long as the SM with the most targets, ceil(CTAs / SMs) * block of
+// them against count / SMs on average: 64-thread CTAs cut that rounding loss (N = 65536 on 148 SMs:
+// 4 x 128 = 512 targets on the fullest SM vs 7 x 64 = 448, average 443).
+static void auto_shape(int count, int sms, int *block, int *unroll, int *warps) {
+    *block = 128; *unroll = 2; *warps = 24;
+    if (sms <= 0) return;
+    const long ctas128 = (count + 127) / 128, ctas64 = (count + 63) / 64;
+    if (ctas128 >= 6L * sms) return;                         // a full wave or more
+    const long worst128 = (ctas128 + sms - 1) / sms * 128, worst64 = (ctas64 + sms - 1) / sms * 64;
+    if (worst64 < worst128 && ctas64 <= 14L * sms) { *block = 64; *warps = 28; }
+}
+
 static int launch_step(const hgb_nbody *h, const NbShard &s, const double *src, int t0, int count,
                        const int *tlist, const PeerOut &out, double *out_list,
                        const int *run_if = nullptr) {
     if (count <= 0) return HGB_OK;
     const bool fast = h->mode == HGB_NBODY_FAST;
-    const int block = h->block ? h->block : 128;
-    const int unroll = h->unroll ? h->unroll : 2;
-    const int warps = h->warps ? h->warps : 24;   // measured on B200: 24 >= 32 > 40 (profiles/r1_nbody_sweep.txt)
+    int block = 0, unroll = 0, warps = 0;
+    auto_shape(count, s.dev->sms, &block, &unroll, &warps);
+    if (h->block) { block = h->block; if (!h->warps && block != 64) warps = 24; }
+    if (h->unroll) unroll = h->unroll;
+    if (h->warps) warps = h->warps;
     const int grid = (count + block - 1) / block;
     cudaStream_t st = s.dev->stream;
 #define HGB_V(B, U, W)                                                                             \
@@ -76,6 +92,7 @@ static int launch_step(const hgb_nbody *h, const NbShard &s, const double *src, 
     HGB_VW(128, 1) HGB_VW(128, 2) HGB_VW(128, 4)
     HGB_V(128, 1, 28) HGB_V(128, 2, 28) HGB_V(128, 4, 28)   // 7 CTAs per SM: 1036 slots
     HGB_VW(256, 1) HGB_VW(256, 2) HGB_VW(256, 4)
+    HGB_V(64, 2, 28) HGB_V(64, 2, 24) HGB_V(64, 4, 24) HGB_V(64, 1, 28)   // small target counts
 #undef HGB_VW
 #undef HGB_V
     set_error("no nbody kernel variant block=%d unroll=%d warps=%d", block, unroll, warps);
@@ -104,8 +121,15 @@ static int launch_sym_variant(cudaStream_t st, int sms, const double *src, int n
     return HGB_OK;
 }
 
+// The hand-off tag is (epoch << 21) | (worker + 1): the worker count ceil(n / (32 R)) must stay below
+// 2^21 or worker ids spill into the epoch bits and tags of different workers alias (R >= 1, so
+// n < 2^26 is safe for every variant); larger sets take the standard kernel.
+constexpr int kSymMaxN = 1 << 26;
+static_assert((kSymMaxN / 32) < (1 << 21) + 1, "worker id must fit the 21-bit tag field");
+
 static bool sym_applies(const hgb_nbody *h) {
-    return h->sym != 0 && h->world == 1 && h->mode == HGB_NBODY_EXACT && h->n >= h->sym_min_n;
+    return h->sym != 0 && h->world == 1 && h->mode == HGB_NBODY_EXACT && h->n >= h->sym_min_n &&
+           h->n < kSymMaxN;
 }
 
 // whole step on shard s: tickets/flags reset, wavefront kernel, G*acc, conditional redo
@@ -300,10 +324,15 @@ int hgb_nbody_config(hgb_nbody *h, int mode, int exchange) {
 
 int hgb_nbody_tune(hgb_nbody *h, int block, int unroll, int warps) {
     HGB_ARG(h, "handle");
-    HGB_ARG(block == 0 || block == 128 || block == 256, "block in {128,256}");
+    HGB_ARG(block == 0 || block == 64 || block == 128 || block == 256, "block in {64,128,256}");
     HGB_ARG(unroll == 0 || unroll == 1 || unroll == 2 || unroll == 4, "unroll in {1,2,4}");
     HGB_ARG(warps == 0 || warps == 24 || warps == 28 || warps == 32 || warps == 40, "warps in {24,28,32,40}");
-    HGB_ARG(warps != 28 || block != 256, "warps = 28 needs 128-thread CTAs");
+    HGB_ARG(warps != 28 || block != 256, "warps = 28 needs 64- or 128-thread CTAs");
+    if (block == 64) {
+        const int u = unroll ? unroll : 2, w = warps ? warps : 28;
+        HGB_ARG((u == 2 && (w == 28 || w == 24)) || (u == 4 && w == 24) || (u == 1 && w == 28),
+                "64-thread CTAs: (unroll, warps) in {(2,28), (2,24), (4,24), (1,28)}");
+    }
     h->block = block;
     h->unroll = unroll;
     h->warps = warps;
@@ -375,7 +404,7 @@ static int nb_advance(hgb_nbody *h, int iterations, float *ms, bool dyn) {
         } else if (multi) {
             HGB_NCCL(nccl().GroupStart());
             for (NbShard &s : h->sh) {
-                ncclComm_t comm = h->rank_mode ? rt().rank_comm : s.dev->comm;
+                ncclComm_t comm = h->rank_mode ? rt().rank_comm : sp_comm(h->world, s.index);
                 for (int c = 0; c < 3; ++c) {
                     double *recv = s.state[nxt] + (size_t)c * h->npad;
                     HGB_NCCL(nccl().AllGather(recv + (size_t)s.index * h->slice, recv, h->slice,

@@ -43,8 +43,10 @@ int hgb_init(void);                          /* optional; everything initialises
 void hgb_finalize(void);                     /* frees streams, staging, communicators */
 unsigned long long hgb_launch_count(void);   /* kernels launched by this library so far */
 int hgb_flush_l2(void);                      /* overwrite a buffer larger than L2 on every local device */
-/* measured roofline denominators (bench.py; each takes well under a second) */
-int hgb_measure_fp64_peak(double *tflops, double *sm_mhz_est); /* dependent-free DFMA loop */
+/* measured roofline denominators (bench.py).  The FP64 probe is a dependent-free DFMA loop (8 chains
+ * per thread) sustained for ~1 s after a warm-up, so that it reads the settled SM clock;
+ * *sm_mhz_est = the clock that rate implies at 64 DFMA lanes per SM per cycle. */
+int hgb_measure_fp64_peak(double *tflops, double *sm_mhz_est);
 int hgb_measure_hbm_copy(double *gbs);                         /* device copy, read+write bytes */
 
 /* ---- one process per GPU (torchrun): communicator over NCCL ------------ */
@@ -83,8 +85,10 @@ int hgb_nbody_create(hgb_nbody **out, int n, int ngpus);
 /* one process per GPU: this rank owns target shard hgb_comm_rank() of hgb_comm_world() */
 int hgb_nbody_create_rank(hgb_nbody **out, int n);
 int hgb_nbody_config(hgb_nbody *h, int mode, int exchange);
-/* kernel variant; 0 = default: threads per CTA {128,256}, sources per unrolled group/2 {1,2,4},
- * resident warps per SM the register allocation allows {24,28,32,40} (28: 128-thread CTAs only) */
+/* kernel variant; 0 = automatic (128-thread CTAs, 6 per SM; 64-thread CTAs when the target count is
+ * below one wave and they balance better over the SMs): threads per CTA {64,128,256}, sources per
+ * unrolled group/2 {1,2,4}, resident warps per SM the register allocation allows {24,28,32,40}
+ * (28: 64/128-thread CTAs; 64-thread CTAs: (unroll, warps) in {(2,28), (2,24), (4,24), (1,28)}) */
 int hgb_nbody_tune(hgb_nbody *h, int block, int unroll, int warps);
 /* Pair-symmetric EXACT step (csrc/nbody_sym.cuh): every unordered pair is evaluated once and added to
  * both bodies, each target still summing its sources in the order of accel() (src/nbody/nbody-run.c:

@@ -91,6 +91,12 @@ def test_binary_round_trip_and_layout(tmp_path):
         cv.read_image_binary(tmp_path / "short.hgb")
     with pytest.raises(HgbError):
         cv.read_image_binary(tmp_path / "k.txt")
+    # a crafted header must not size the allocation: huge extents are refused before malloc
+    # (2^31-1 squared * 8 overflows size_t arithmetic on the element count times 8)
+    for h, w in ((0x7fffffff, 0x7fffffff), (1 << 20, 1 << 20), (5, 38)):
+        (tmp_path / "evil.hgb").write_bytes(b"HGBIMG1\n" + struct.pack("<ii", h, w) + raw[16:])
+        with pytest.raises(HgbError):
+            cv.read_image_binary(tmp_path / "evil.hgb")
 
 
 def test_against_the_reference_parser_when_built(tmp_path):

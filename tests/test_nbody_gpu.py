@@ -81,13 +81,22 @@ def test_every_kernel_variant_gives_the_same_bits(hgb):
     pos = synth.plummer(n, seed=7)
     want = np.zeros_like(pos)
     port.nbody_step_range(pos, want, 0, n)
-    for block in (128, 256):
-        for unroll in (1, 2, 4):
-            for warps in (24, 32, 40):
-                with hgb.nbody.NBody(n) as nb:
-                    nb.tune(block, unroll, warps).upload(pos)
-                    nb.step(1)
-                    assert np.array_equal(nb.download(), want), (block, unroll, warps)
+    shapes = [(b, u, w) for b in (128, 256) for u in (1, 2, 4) for w in (24, 32, 40)]
+    shapes += [(128, 2, 28), (64, 2, 28), (64, 2, 24), (64, 4, 24), (64, 1, 28)]   # 64: small target counts
+    for block, unroll, warps in shapes:
+        with hgb.nbody.NBody(n) as nb:
+            nb.tune(block, unroll, warps).upload(pos)
+            nb.step(1)
+            assert np.array_equal(nb.download(), want), (block, unroll, warps)
+    # the automatic shape (64-thread CTAs below one wave) on ragged counts around the tile sizes
+    for m in (1, 63, 64, 65, 255, 257, 511, 513, 2999):
+        sub = np.ascontiguousarray(pos[:m])
+        w2 = np.zeros_like(sub)
+        port.nbody_step_range(sub, w2, 0, m)
+        with hgb.nbody.NBody(m) as nb:
+            nb.symmetric(0, 0).upload(sub)
+            nb.step(1)
+            assert np.array_equal(nb.download(), w2), m
 
 
 def test_overflow_and_nonfinite_operands_take_the_ieee_slow_path(hgb):

@@ -37,6 +37,18 @@ def test_reference_nbody_gtest_suite():
     assert r.returncode == 0 and "[  PASSED  ] 3 tests." in r.stdout
 
 
+@pytest.mark.parametrize("exe_name", ["nbody_symbols_b200", "conv_symbols_b200"])
+def test_every_declared_symbol_matches_the_reference_object_code(exe_name):
+    """pair_wise_accel / accel / run and apply_kernel_to_padded_point / apply_kernel_to_padded_image /
+    run_on_padded_image (reference src/nbody/nbody-run.h:23,34,46, src/convolution/convolution-run.h:
+    45-46,58-60,70-71): the shim's symbol and the reference's own compiled function (renamed ref_*)
+    in one binary, bit for bit (shim/test/symbols_*.c)."""
+    exe = _need(exe_name)
+    r = subprocess.run([exe], cwd=CWD, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert "PASSED" in r.stdout and " 0 mismatches" in r.stdout
+
+
 @pytest.mark.parametrize("args", [["-s", "3", "-n", "10"], ["-s", "3", "-n", "2"], ["-s", "3", "-n", "3"]])
 def test_reference_nbody_main_on_gpu(golden, args):
     """src/nbody.c as shipped (defaults: 3 bodies, 10 iterations, 10 repetitions) -> ../nbody.res"""
