@@ -5,10 +5,15 @@
   torchrun --nnodes=1 --nproc-per-node N ... bench.py --gpus N --steps K --warmup W
 
 One "step" = one all-pairs FP64 nbody step over N = 2^20 bodies (BASELINE.json configs[3]),
-EXACT mode (bit-identical to the reference).  Rank 0 prints ONE JSON line.  The second
-benchmark kernel (16384^2 2D convolution, 3x3 and 7x7, configs[4]) is reported in the
-same line under "conv".  `--impl reference` times the unmodified reference (oracle/_ref,
-else the oracle port) on the host cores for the same metric.
+EXACT mode (bit-identical to the reference).  Rank 0 prints ONE JSON line.  The same line carries
+  * "parity_check": after the timed region every rank compares its results with the oracle (a target
+    sample of the last nbody step; row bands of the convolution results incl. the band seams) --
+    a mismatch makes the run exit non-zero;
+  * "nbody_64k_plummer_100" (configs[2]), "nbody_1m_plummer" (SURVEY 8d item 4);
+  * "conv": 16384^2 images, 3x3 / 7x7 dense (configs[4]), the shipped 5x5 kernel.txt, an integer image;
+  * "cpu_baseline" (N=1): the unmodified reference on the host cores.
+`--impl reference` times the unmodified reference (oracle/_ref, else the oracle port) on the host
+cores for the same metric.
 """
 import argparse
 import json
@@ -26,13 +31,14 @@ import numpy as np  # noqa: E402
 OUT = sys.stdout
 N_BODIES = 1 << 20
 CONV_N = 16384
-CONV_ITERS = 10          # the config's iteration count (used by the end-to-end leg)
+CONV_ITERS = 10          # the config's iteration count (used by the end-to-end leg and its parity check)
 CONV_TIMED = 100         # device-resident timing runs 10 x 10 iterations back to back: at 8 GPUs ten
                          # iterations last ~1 ms, comparable to the host skew between ranks after a barrier
 FLOP_PER_INTERACTION = 19          # 3 sub, 3 mul+3 add (+EPS), 2 mul, sqrt, div, 3 mul+3 add
 FP64_INSTR_PER_INTERACTION = 29    # exact mode: 17 plain + 8 (IEEE sqrt) + 4 (IEEE reciprocal) FP64-pipe ops (tools/sass_loop.py)
-FP64_INSTR_PER_INTERACTION_SYM = 16  # pair-symmetric kernel: 26 + 3 + 3 FP64-pipe ops per PAIR = 2 interactions
 BYTES_PER_PIXEL = 16               # 8 B read + 8 B written per inner pixel per iteration
+PARITY_TARGETS = 256
+PARITY_BAND = 64
 
 
 def workload(n):
@@ -69,6 +75,7 @@ class ClockSampler:
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
             self.proc = None
+        return self
 
     def _read(self):
         for line in self.proc.stdout:
@@ -114,6 +121,29 @@ def pinned(shape):
 
 
 # ---------------------------------------------------------------------------------------------
+# CPU side: the unmodified reference (oracle/_ref) where it was built, else the oracle port
+def reference_builds(step, n_cal=8192):
+    """interactions/s of every build of the reference that runs on this host (one warm + one timed
+    step over n_cal bodies); {} when only the port exists"""
+    from hg_c_benchmarks_b200 import synth
+    from oracle import ref
+    rates = {}
+    if not ref.available():
+        return rates
+    cal = synth.uniform_cube(n_cal, seed=1)
+    buf = np.zeros_like(cal)
+    for variant in ref.VARIANTS:
+        if not ref.available(variant):
+            continue
+        ref.use(variant)
+        step(cal, buf)
+        t0 = time.perf_counter()
+        step(cal, buf)
+        rates[variant] = float(n_cal) ** 2 / (time.perf_counter() - t0)
+    ref.use("")
+    return rates
+
+
 def run_reference(args):
     """the reference's own CPU implementation on the host cores, bounded sample"""
     rank, _, world = env_rank()
@@ -131,26 +161,21 @@ def run_reference(args):
         else:
             port.nbody_run(pos, buf, 1, cores)
 
-    # calibrate so one step is a few seconds of wall time; where the -O3 + profile-feedback build
-    # of the reference (what pgo.sh intended, oracle/Makefile ref-pgo) exists, the faster of the
-    # two builds on this host is the one timed
-    cal = synth.uniform_cube(8192, seed=1)
-    buf = np.zeros_like(cal)
-    builds = {}
-    for variant in (("", "_pgo") if use_ref else ("",)):
-        if use_ref:
-            if not ref.available(variant):
-                continue
-            ref.use(variant)
+    # every build of the unmodified reference that runs here is calibrated and the fastest is timed:
+    # shipped flags (x86-64-v3), -O3 + profile feedback (what pgo.sh intended, oracle/Makefile ref-pgo),
+    # and the AVX-512 build (the reference's -march=native on such a host)
+    builds = reference_builds(step)
+    if builds:
+        best = max(builds, key=builds.get)
+        ref.use(best)
+        rate, build_name = builds[best], ref.VARIANTS[best]
+    else:
+        cal = synth.uniform_cube(8192, seed=1)
+        buf = np.zeros_like(cal)
         step(cal, buf)
         t0 = time.perf_counter()
         step(cal, buf)
-        builds[variant] = 8192.0 ** 2 / (time.perf_counter() - t0)
-    best = max(builds, key=builds.get)
-    if use_ref:
-        ref.use(best)
-    rate = builds[best]
-    build_name = {"": "shipped flags (-std=c11 -O2 -fopenmp)", "_pgo": "-O3 + gcc profile feedback (pgo.sh's intent)"}[best]
+        rate, build_name = 8192.0 ** 2 / (time.perf_counter() - t0), "oracle port (oracle/hg_oracle.c), -O2"
     budget_s = 150.0 / max(1, args.steps + args.warmup)
     n = int(min(N_BODIES, max(8192, (rate * min(6.0, budget_s)) ** 0.5))) // 1024 * 1024
     pos = synth.uniform_cube(N_BODIES, seed=1)[:n].copy()     # first n bodies of the same workload
@@ -164,69 +189,153 @@ def run_reference(args):
     value = float(n) * n / dt
     sample = (f"first {n} of the {N_BODIES} bodies, 1 step = {n}^2 interactions per step, "
               f"{args.steps} steps, OpenMP over {cores} host threads; build: {build_name}")
+    caveat = (f" [CPU arm: each step is a bounded sample, the first {n} bodies = {n}^2 interactions; the rate "
+              f"(interactions/s) is size-independent for this O(N^2) loop, a full N={N_BODIES} step would take "
+              f"{float(N_BODIES) ** 2 / value:.0f} s on these {cores} threads]")
     line = {"impl": "reference", "metric": "nbody_fp64_interactions_per_s", "value": value,
             "unit": "interactions/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload(N_BODIES),
+            "config": {"workload": workload(N_BODIES) + caveat,
                        "sample": "CPU arm: a bounded sample of the workload per step, see cpu_baseline.sample"},
-            "cpu_baseline": {"value": value, "unit": "interactions/s", "cores": cores, "kind": kind, "sample": sample},
+            "cpu_baseline": {"value": value, "unit": "interactions/s", "cores": cores, "kind": kind, "sample": sample,
+                             "builds_calibrated": {ref.VARIANTS[k]: v for k, v in builds.items()}},
             "e2e": {"value": value, "unit": "interactions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), file=OUT, flush=True)
 
 
-# ---------------------------------------------------------------------------------------------
 def cpu_baseline():
-    """bounded CPU sample on rank 0 at N=1: the unmodified reference on all host cores"""
+    """bounded CPU samples on rank 0 at N=1: the unmodified reference on all
+    host cores and on one (-p 1); nbody; convolution 3x3 and 7x7 at 4096^2 and one 16384^2 iteration"""
     from hg_c_benchmarks_b200 import synth
     from oracle import port, ref
     cores = port.ncpu()
     use_ref = ref.available()
-    run = (lambda a, b: ref.nbody_run(a, b, 1, cores)) if use_ref else (lambda a, b: port.nbody_run(a, b, 1, cores))
-    cal = synth.uniform_cube(8192, seed=1)
-    buf = np.zeros_like(cal)
-    run(cal, buf)
-    t0 = time.perf_counter()
-    run(cal, buf)
-    rate = 8192.0 ** 2 / (time.perf_counter() - t0)
-    n = int(min(262144, max(16384, (rate * 12.0) ** 0.5))) // 1024 * 1024
+
+    def nb_run(a, b, procs):
+        if use_ref:
+            ref.nbody_run(a, b, 1, procs)
+        else:
+            port.nbody_run(a, b, 1, procs)
+
+    def cv_run(img, prev, w, h, p, k, it, procs):
+        if use_ref:
+            ref.conv_run(img, prev, w, h, p, k, it, procs)
+        else:
+            port.conv_run(img, prev, w, h, p, k, it, procs)
+
+    builds = reference_builds(lambda a, b: nb_run(a, b, cores))
+    rate = builds.get("", None)
+    if rate is None:
+        cal = synth.uniform_cube(8192, seed=1)
+        buf = np.zeros_like(cal)
+        nb_run(cal, buf, cores)
+        t0 = time.perf_counter()
+        nb_run(cal, buf, cores)
+        rate = 8192.0 ** 2 / (time.perf_counter() - t0)
+    n = int(min(262144, max(16384, (rate * 10.0) ** 0.5))) // 1024 * 1024
     pos = synth.uniform_cube(N_BODIES, seed=1)[:n].copy()
     buf = np.zeros_like(pos)
     t0 = time.perf_counter()
-    run(pos, buf)
+    nb_run(pos, buf, cores)
     dt = time.perf_counter() - t0
     out = {"value": float(n) * n / dt, "unit": "interactions/s", "cores": cores,
            "kind": "reference" if use_ref else "port",
            "sample": f"first {n} of the {N_BODIES} bodies, one step ({n}^2 interactions, {dt:.1f} s), "
                      f"reference run() with number_of_processes={cores}",
-           "build": "shipped effective flags: -std=c11 -fcommon -O2 -fopenmp (CMakeLists.txt:40,45)"}
-    if use_ref and ref.available("_pgo"):
-        # the reference's pgo.sh is inert as shipped; its intent (-O3 + profile feedback) is built by
-        # oracle/Makefile ref-pgo from the same unmodified sources and timed on a smaller sample
-        ref.use("_pgo")
-        m = max(8192, n // 2 // 1024 * 1024)
-        q = pos[:m].copy()
-        qb = np.zeros_like(q)
-        t0 = time.perf_counter()
-        ref.nbody_run(q, qb, 1, cores)
-        dq = time.perf_counter() - t0
-        ref.use("")
-        out["pgo"] = {"value": float(m) * m / dq, "unit": "interactions/s",
-                      "build": "-O3 + gcc -fprofile-use trained by the reference CLI (-s 4096 -n 2)",
-                      "sample": f"first {m} bodies, one step ({dq:.1f} s)"}
-    # convolution: 4096^2, 3x3 dense, 2 iterations
-    w = 4096
-    img = synth.add_padding(synth.image_float(w, w, seed=3), 1)
-    prev = np.zeros_like(img)
-    k = synth.kernel_dense(3)
-    conv = (lambda: ref.conv_run(img, prev, w, w, 1, k, 2, cores)) if use_ref else (lambda: port.conv_run(img, prev, w, w, 1, k, 2, cores))
+           "build": "shipped effective flags -std=c11 -fcommon -O2 -fopenmp (CMakeLists.txt:40,45); -march=x86-64-v3 "
+                    "instead of the reference's -march=native so that the binary runs on any host (the AVX-512 "
+                    "and profile-feedback builds are calibrated under `builds`)"}
+    if builds:
+        out["builds"] = {ref.VARIANTS[k]: {"value": v, "unit": "interactions/s", "sample": "8192 bodies, one step"}
+                         for k, v in builds.items()}
+    # -p 1: one host thread (the reference's default)
+    m = 16384
+    q, qb = pos[:m].copy(), np.zeros((m, 3))
     t0 = time.perf_counter()
-    conv()
+    nb_run(q, qb, 1)
+    d1 = time.perf_counter() - t0
+    out["p1"] = {"value": float(m) * m / d1, "unit": "interactions/s", "cores": 1,
+                 "sample": f"first {m} bodies, one step ({d1:.1f} s), number_of_processes=1"}
+    # convolution: 4096^2, dense 3x3 and 7x7, 2 iterations, all cores; 3x3 also on one thread
+    w = 4096
+    dense = synth.image_float(w, w, seed=3)
+    conv = {}
+    for k in (3, 7):
+        p = k // 2
+        img = synth.add_padding(dense, p)
+        prev = np.zeros_like(img)
+        kern = synth.kernel_dense(k)
+        t0 = time.perf_counter()
+        cv_run(img, prev, w, w, p, kern, 2, cores)
+        dtc = time.perf_counter() - t0
+        conv[f"{k}x{k}"] = {"value": w * w * 2 * BYTES_PER_PIXEL / dtc / 1e9, "unit": "GB/s", "cores": cores,
+                            "sample": f"{w}x{w} dense {k}x{k}, 2 iterations, run_on_padded_image with {cores} threads"}
+    img = synth.add_padding(dense[:1024], 1)
+    prev = np.zeros_like(img)
+    t0 = time.perf_counter()
+    cv_run(img, prev, w, 1024, 1, synth.kernel_dense(3), 2, 1)
     dtc = time.perf_counter() - t0
-    out["conv"] = {"value": w * w * 2 * BYTES_PER_PIXEL / dtc / 1e9, "unit": "GB/s",
-                   "sample": f"{w}x{w} 3x3 dense, 2 iterations, run_on_padded_image with {cores} threads"}
+    conv["3x3_p1"] = {"value": w * 1024 * 2 * BYTES_PER_PIXEL / dtc / 1e9, "unit": "GB/s", "cores": 1,
+                      "sample": f"{w}x1024 dense 3x3, 2 iterations, one thread"}
+    del dense, img, prev
+    # one iteration at the benchmark size (2 x 2 GiB padded images on the host)
+    try:
+        big = synth.add_padding(synth.image_float(CONV_N, CONV_N, seed=3), 1)
+        prev = np.zeros_like(big)
+        t0 = time.perf_counter()
+        cv_run(big, prev, CONV_N, CONV_N, 1, synth.kernel_dense(3), 1, cores)
+        dtc = time.perf_counter() - t0
+        conv["3x3_16k"] = {"value": CONV_N * CONV_N * BYTES_PER_PIXEL / dtc / 1e9, "unit": "GB/s", "cores": cores,
+                           "sample": f"{CONV_N}x{CONV_N} dense 3x3, ONE iteration ({dtc:.2f} s), {cores} threads"}
+        del big, prev
+    except MemoryError:
+        conv["3x3_16k"] = None
+    out["conv"] = conv["3x3"]
+    out["conv_all"] = conv
     return out
+
+
+# ---------------------------------------------------------------------------------------------
+# parity: the oracle as the checker, outside every timed region
+def nbody_parity(nb, n, world, rank, seed):
+    """compare a target sample of the LAST step (state k from state k-1, both still on the device)
+    with the oracle's accel(); returns (ok, targets checked)"""
+    from hg_c_benchmarks_b200 import dist as hdist
+    from oracle import port
+    cur, prev = nb.download(want_prev=True)
+    s = hdist.nbody_slice(n, world)
+    seams = [t for r in range(world) for t in (r * s - 1, r * s) if 0 <= t < n]
+    rng = np.random.default_rng(seed + 1000 * rank)
+    sample = np.unique(np.concatenate([rng.choice(n, min(n, PARITY_TARGETS), replace=False),
+                                       np.array(seams + [0, n - 1])])).astype(np.int32)
+    want = port.nbody_accel_subset(prev, sample)
+    return bool(np.array_equal(cur[sample], want)), int(sample.size)
+
+
+def conv_parity(got, dense, r0, rows, cn, p, kern, iters):
+    """rows of this rank's band after `iters` iterations against the oracle run on a sub-image with an
+    iters*p-row margin (pollution from the sub-image's artificial edges travels p rows per iteration;
+    true image edges are the sub-image's own edges and clamp like the reference's).  Bands: the first
+    PARITY_BAND rows of the band, its last ones (both touch the neighbours' halos = the band seams) and
+    one in the middle.  Returns (ok, rows checked)"""
+    from hg_c_benchmarks_b200 import synth
+    from oracle import port
+    if rows <= 0:
+        return True, 0
+    m = iters * p
+    nb = min(PARITY_BAND, rows)
+    starts = sorted({r0, r0 + max(0, rows // 2 - nb // 2), r0 + rows - nb})
+    ok, checked = True, 0
+    for a in starts:
+        lo, hi = max(0, a - m), min(cn, a + nb + m)
+        sub = synth.add_padding(dense[lo:hi], p)
+        tmp = np.zeros_like(sub)
+        port.conv_run(sub, tmp, cn, hi - lo, p, kern, iters)
+        ok = ok and bool(np.array_equal(got[a - r0:a - r0 + nb], sub[a - lo:a - lo + nb]))
+        checked += nb
+    return ok, checked
 
 
 def main():
@@ -245,6 +354,7 @@ def main():
     ap.add_argument("--conv-size", type=int, default=CONV_N, help=argparse.SUPPRESS)
     ap.add_argument("--skip-conv", action="store_true", help=argparse.SUPPRESS)
     ap.add_argument("--skip-cpu", action="store_true", help=argparse.SUPPRESS)
+    ap.add_argument("--skip-extra", action="store_true", help=argparse.SUPPRESS)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":
@@ -275,26 +385,44 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    def all_ok(ok):
+        if not dist:
+            return bool(ok)
+        t = torch.tensor([1.0 if ok else 0.0], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        return bool(t.item() > 0.5)
+
+    def total(x):
+        if not dist:
+            return x
+        t = torch.tensor([float(x)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return int(t.item())
+
     peaks = measured_peaks()
+    sms = torch.cuda.get_device_properties(local_rank).multi_processor_count
+    # FP64 issue-rate probe: ~1 s of dependent-free DFMAs after a warm-up, clocks sampled meanwhile
+    probe_sampler = ClockSampler(local_rank).start() if rank == 0 else None
     tf, mhz, gbs = C.c_double(), C.c_double(), C.c_double()
     H._abi.check(L.hgb_measure_fp64_peak(C.byref(tf), C.byref(mhz)))
+    probe_clocks = probe_sampler.stop() if probe_sampler else None
     H._abi.check(L.hgb_measure_hbm_copy(C.byref(gbs)))
 
     n = args.bodies
     pos_np, pos_t = pinned((n, 3))
     pos_np[...] = synth.uniform_cube(n, seed=1)
     out_np, out_t = pinned((n, 3))
+    parity = {}
 
     # ---------------- nbody: device-resident steps -------------------------------------------
     nb = H.nbody.NBody(n, ngpus=None, mode=H.NBODY_EXACT)
     nb.upload(pos_np)
     sym = int(L.hgb_nbody_symmetric(nb._h))      # pair-symmetric variant in use (0: standard kernel)
-    fp64_instr = FP64_INSTR_PER_INTERACTION_SYM if sym else FP64_INSTR_PER_INTERACTION
-    nb_kernel = f"nbody_sym_kernel<{sym // 100},{sym // 10 % 10},{sym % 10}>" if sym else "nbody_step_kernel<128,2,24,false>"
+    fp64_instr = float(L.hgb_nbody_fp64_instr(nb._h))
+    nb_kernel, nb_parallelism = nb.describe()
     for _ in range(args.warmup):
         nb.step(1)
     sampler = ClockSampler(local_rank)
-    launches0 = L.hgb_launch_count()
     barrier()
     if rank == 0:
         sampler.start()
@@ -311,6 +439,8 @@ def main():
     clocks = sampler.stop() if rank == 0 else None
     ms_per_step = max_over_ranks(sum(step_ms) / len(step_ms))
     value = float(n) * n / (ms_per_step * 1e-3)
+    ok, cnt = nbody_parity(nb, n, world, rank, seed=1)         # outside the timed region
+    parity["nbody"] = {"ok": all_ok(ok), "targets": total(cnt), "of": "last timed step, every rank's copy"}
 
     # ---------------- nbody: end to end through the public call, host buffers ----------------
     e2e_steps = max(1, min(args.steps, 2))
@@ -332,7 +462,7 @@ def main():
     nb.close()
 
     # like-for-like scaling base: when N=1 runs the pair-symmetric kernel, also time the standard
-    # (one target per thread) kernel that the multi-GPU runs use, same inputs, 1 warm-up + 1 step
+    # (one target per thread) kernel, same inputs, 1 warm-up + 1 step
     standard = None
     if sym and world == 1:
         with H.nbody.NBody(n, ngpus=None, mode=H.NBODY_EXACT) as nb_std:
@@ -342,14 +472,50 @@ def main():
             std_ms = nb_std.step(1)
         standard = {"kernel": "nbody_step_kernel<128,2,24,false>", "value": float(n) * n / (std_ms * 1e-3),
                     "unit": "interactions/s", "ms_per_step": std_ms, "steps": 1,
-                    "note": "the kernel every rank runs at N > 1 (targets sharded); scaling of that kernel is value(N) / this"}
+                    "fp64_instr_per_interaction": FP64_INSTR_PER_INTERACTION,
+                    "note": "one target per thread, every interaction evaluated from both sides"}
 
-    # ---------------- convolution 16384^2, 3x3 and 7x7 ----------------------------------------
+    # ---------------- nbody: the other body sets of BASELINE.json / SURVEY 8(d) ----------------
+    extra = {}
+    if not args.skip_extra:
+        for key, m, steps, gen, desc in (
+                ("nbody_64k_plummer_100", 65536, 100, lambda: synth.plummer(65536, seed=1234),
+                 "N=65536 Plummer sphere seed 1234, 100 device-resident steps (BASELINE configs[2])"),
+                ("nbody_1m_plummer", N_BODIES, 2, lambda: synth.plummer(N_BODIES, seed=2),
+                 "N=1048576 Plummer sphere seed 2 (SURVEY 8d item 4)")):
+            if n != N_BODIES and m == N_BODIES:
+                continue
+            p0 = gen()
+            with H.nbody.NBody(m, ngpus=None, mode=H.NBODY_EXACT) as nbx:
+                nbx.upload(p0)
+                nbx.step(1)
+                nbx.upload(p0)
+                barrier()
+                H._abi.check(L.hgb_flush_l2())
+                msx = max_over_ranks(nbx.step(steps))
+                okx, cntx = nbody_parity(nbx, m, world, rank, seed=m)
+                kernx = nbx.describe()[0]
+                instrx = float(L.hgb_nbody_fp64_instr(nbx._h))
+            parity[key] = {"ok": all_ok(okx), "targets": total(cntx), "of": f"step {steps}"}
+            extra[key] = {"value": float(m) * m * steps / (msx * 1e-3), "unit": "interactions/s",
+                          "ms_per_step": msx / steps, "steps": steps, "workload": desc,
+                          "kernel": kernx, "fp64_instr_per_interaction": instrx}
+            del p0
+
+    # ---------------- convolution 16384^2 ------------------------------------------------------
     conv = {}
     if not args.skip_conv:
         cn = args.conv_size
-        dense = synth.image_float(cn, cn, seed=3)
-        for k in (3, 7):
+        cases = [("3x3", 3, synth.kernel_dense(3), "float"), ("7x7", 7, synth.kernel_dense(7), "float")]
+        if not args.skip_extra:
+            cases += [("5x5_kernel_txt", 5, synth.KERNEL_TXT.copy(), "float"),
+                      ("3x3_int_image", 3, synth.kernel_dense(3), "int")]
+        dense, dense_kind = None, None
+        for key, k, kern, kind in cases:
+            if kind != dense_kind:
+                del dense
+                dense = synth.image_float(cn, cn, seed=3) if kind == "float" else synth.image_int(cn, cn, seed=4)
+                dense_kind = kind
             p = k // 2
             cv = H.convolution.Conv2D(cn, cn, p, ngpus=None)
             r0, rows = cv.band()
@@ -357,10 +523,12 @@ def main():
             got, got_t = pinned((rows, cn + 2 * p))
             if rows:
                 band[...] = synth.add_padding(dense[r0:r0 + rows], p)
-            cv.set_kernel(synth.kernel_dense(k)).upload(band)
+            cv.set_kernel(kern).upload(band)
             cv.step(3)
             barrier()
+            l0 = L.hgb_launch_count()
             ms = max_over_ranks(cv.step(CONV_TIMED))          # inputs (2 GiB) >> L2: no flush needed
+            conv_launches = L.hgb_launch_count() - l0
             barrier()
             t0 = time.perf_counter()                          # e2e: H2D band, iterations, D2H band
             cv.upload(band)
@@ -369,6 +537,9 @@ def main():
             barrier()
             e2e = max_over_ranks((time.perf_counter() - t0) * 1e3)
             cv.close()
+            okc, cntc = conv_parity(got, dense, r0, rows, cn, p, kern, CONV_ITERS)
+            parity[f"conv_{key}"] = {"ok": all_ok(okc), "rows": total(cntc),
+                                     "of": f"{CONV_ITERS} iterations (the e2e leg's result), 3 bands of <= {PARITY_BAND} rows per rank incl. band seams"}
             del band, got, band_t, got_t
             gbps = cn * cn * BYTES_PER_PIXEL * CONV_TIMED / (ms * 1e-3) / 1e9
             peak = peaks.get("hbm_gbs", 6650.0)
@@ -378,9 +549,11 @@ def main():
             per_launch = 2 if k == 3 else 1
             traffic = ncu_traffic("conv3_fused2_kernel" if k == 3 else f"conv_stream_kernel<{k},")
             launch_ms = ms / CONV_TIMED * per_launch
+            image_desc = "uniform [0,1) doubles seed 3" if kind == "float" else "integer-valued doubles 0..255 seed 4"
+            kern_desc = "the shipped kernel.txt (5x5, 5 non-zero taps)" if key == "5x5_kernel_txt" else f"dense {k}x{k} seed 5"
             entry = {"metric": "conv2d_achieved_GBps", "value": gbps, "unit": "GB/s",
-                     "ms_per_iteration": ms / CONV_TIMED, "iterations": CONV_TIMED,
-                     "workload": f"{cn}x{cn} uniform [0,1) doubles seed 3, dense {k}x{k} seed 5, row bands over {world} GPU(s)",
+                     "ms_per_iteration": ms / CONV_TIMED, "iterations": CONV_TIMED, "gpu_launches": int(conv_launches),
+                     "workload": f"{cn}x{cn} {image_desc}, {kern_desc}, row bands over {world} GPU(s)",
                      "e2e_GBps": cn * cn * BYTES_PER_PIXEL * CONV_ITERS / (e2e * 1e-3) / 1e9,
                      "roofline": {"bound": "hbm", "achieved": gbps / world, "peak": peak,
                                   "unit": "GB/s", "frac": gbps / world / peak,
@@ -394,13 +567,21 @@ def main():
                                   "per_gpu": True}}
             if k >= 5:   # 2*K^2 unfused FP64 ops per pixel make 5x5/7x7 FP64-pipe bound
                 ops = 2.0 * k * k * cn * cn * CONV_TIMED / (ms * 1e-3) / world
-                entry["roofline_fp64"] = {"bound": "fp64", "achieved": ops / 1e12, "peak": tf.value / 2,
-                                          "unit": "T FP64-instr/s", "frac": ops / 1e12 / (tf.value / 2),
+                issue = sms * 64.0 * (clocks["sm_mhz"] if clocks and clocks.get("sm_mhz") else peaks.get("sm_max_mhz", 1965.0)) * 1e6
+                entry["roofline_fp64"] = {"bound": "fp64", "achieved": ops / 1e12, "peak": issue / 1e12,
+                                          "unit": "T FP64-instr/s", "frac": ops / issue,
+                                          "frac_of_probe": ops / 1e12 / (tf.value / 2),
+                                          "peak_source": "clock-true issue rate: SMs x 64 lanes x SM clock sampled during the nbody steps",
                                           "note": "exact mode needs a DMUL and a DADD per tap (no FMA)"}
-            conv[f"{k}x{k}"] = entry
+            conv[key] = entry
         del dense
 
     if rank == 0:
+        sm_mhz = clocks["sm_mhz"] if clocks and clocks.get("sm_mhz") else None
+        clock_true_tf = sms * 64 * 2 * sm_mhz * 1e6 / 1e12 if sm_mhz else None
+        issue_rate = sms * 64 * sm_mhz * 1e6 if sm_mhz else tf.value / 2 * 1e12
+        per_gpu = value / world
+        all_parity_ok = all(v["ok"] for v in parity.values())
         line = {
             "metric": "nbody_fp64_interactions_per_s", "value": value, "unit": "interactions/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
@@ -408,7 +589,7 @@ def main():
             "data": "synthetic",
             "config": {"workload": workload(n),
                        "kernel": nb_kernel,
-                       "parallelism": f"targets sharded over {world} GPU(s), ncclAllGather of positions per step",
+                       "parallelism": f"{world} GPU(s): {nb_parallelism}",
                        "l2": "512 MiB fill between timed steps (nbody); convolution inputs (2 GiB) exceed L2",
                        "timing": "CUDA events on the library stream per step, max over ranks"},
             "wall_ms_per_step_incl_flush": wall_ms / args.steps,
@@ -418,29 +599,46 @@ def main():
                             else "hgb_nbody_upload + hgb_nbody_step + hgb_nbody_download per rank"},
             "gpu_launches": int(launches_timed),
             "clocks": clocks,
-            "roofline": {"bound": "fp64", "achieved": value / world * FLOP_PER_INTERACTION / 1e12, "peak": tf.value,
-                         "unit": "TFLOP/s", "frac": value / world * FLOP_PER_INTERACTION / 1e12 / tf.value,
+            "parity_check": dict(parity, all_ok=all_parity_ok,
+                                 checker="oracle/hg_oracle.c (C restatement pinned to the unmodified reference), bit-identical required"),
+            "roofline": {"bound": "fp64", "achieved": per_gpu * FLOP_PER_INTERACTION / 1e12,
+                         "peak": clock_true_tf if clock_true_tf else tf.value,
+                         "unit": "TFLOP/s",
+                         "frac": per_gpu * FLOP_PER_INTERACTION / 1e12 / (clock_true_tf if clock_true_tf else tf.value),
                          "kernel": nb_kernel,
-                         "traffic": ncu_traffic("nbody_sym_kernel<" if sym else "nbody_step_kernel<"),
-                         "traffic_note": ("ncu dram bytes per launch (profiles/ncu_traffic.json): positions (24 MiB) stay in L2; the bytes are "
-                                          "evictions of the tagged chain words handed between workers, ~1 GB/s, <0.02 % of HBM bandwidth")
-                                         if sym else "ncu dram bytes per launch (profiles/ncu_traffic.json): the 24 MiB of positions stay in L2",
+                         "traffic": ncu_traffic("nbody_sym" if sym else "nbody_step_kernel<"),
+                         "traffic_note": "ncu dram bytes per launch (profiles/ncu_traffic.json); positions (24 MiB) and hand-off words live in L2",
                          "per_gpu": True,
-                         "peak_source": "in-run dependent-free DFMA probe (MEASURED_PEAKS.json has no FP64 figure)",
-                         "fp64_pipe_util": value / world * fp64_instr / (tf.value / 2 * 1e12),
-                         "fp64_pipe_util_note": f"{fp64_instr} FP64-pipe instructions per interaction in exact mode (SASS count) vs measured DFMA issue rate",
-                         "probe_sm_mhz": mhz.value, "hbm_copy_probe_gbs": gbs.value},
+                         "peak_source": ("clock-true FP64 rate: SMs x 64 DFMA lanes x 2 flop x the SM clock sampled by nvidia-smi during "
+                                         "the timed steps (MEASURED_PEAKS.json has no FP64 figure)") if clock_true_tf
+                                        else "sustained DFMA probe (no clock samples)",
+                         "peak_clock_true": clock_true_tf, "peak_probe": tf.value,
+                         "probe": {"tflops": tf.value, "implied_sm_mhz": mhz.value, "clocks_during_probe": probe_clocks,
+                                   "what": "~1 s of back-to-back dependent-free DFMA launches after 0.2 s of warm-up (hgb_measure_fp64_peak)"},
+                         "frac_of_probe": per_gpu * FLOP_PER_INTERACTION / 1e12 / tf.value,
+                         "fp64_instr_per_interaction": fp64_instr,
+                         "fp64_pipe_util": per_gpu * fp64_instr / issue_rate,
+                         "fp64_pipe_util_of_probe": per_gpu * fp64_instr / (tf.value / 2 * 1e12),
+                         "fp64_pipe_util_note": (f"{fp64_instr:g} FP64-pipe instructions per interaction (SASS count, tools/sass_loop.py) x "
+                                                 "interactions/s over the clock-true issue rate SMs x 64 x SM clock; comparable to ncu "
+                                                 "sm__pipe_fp64_cycles_active (profiles/)"),
+                         "sms": sms, "hbm_copy_probe_gbs": gbs.value},
             "conv": conv,
         }
+        line.update(extra)
         if standard:
             line["nbody_standard_kernel"] = standard
         if world == 1 and not args.skip_cpu:
             line["cpu_baseline"] = cpu_baseline()
         print(json.dumps(line), file=OUT, flush=True)
+        if not all_parity_ok:
+            print("PARITY MISMATCH: " + json.dumps(parity), file=sys.stderr, flush=True)
     barrier()
     L.hgb_finalize()
     if dist:
         dist.destroy_process_group()
+    if not all(v["ok"] for v in parity.values()):
+        sys.exit(3)
 
 
 if __name__ == "__main__":

@@ -209,6 +209,34 @@ int hgb_nbody_set_symmetric(hgb_nbody *h, int variant, int min_n) {
 
 int hgb_nbody_symmetric(const hgb_nbody *h) { return h && sym_applies(h) ? h->sym : 0; }
 
+int hgb_nbody_describe(const hgb_nbody *h, char *buf, int capacity) {
+    HGB_ARG(h && buf && capacity > 0, "handle / buffer");
+    char kern[160];
+    const bool fast = h->mode == HGB_NBODY_FAST;
+    if (sym_applies(h)) {
+        snprintf(kern, sizeof kern, "nbody_sym_kernel<%d,%d,%d>", h->sym / 100, h->sym / 10 % 10, h->sym % 10);
+    } else {
+        int block = 0, unroll = 0, warps = 0;
+        const int count = h->n < h->slice ? h->n : h->slice;
+        auto_shape(count, h->sh[0].dev->sms, &block, &unroll, &warps);
+        if (h->block) { block = h->block; if (!h->warps && block != 64) warps = 24; }
+        if (h->unroll) unroll = h->unroll;
+        if (h->warps) warps = h->warps;
+        snprintf(kern, sizeof kern, "nbody_step_kernel<%d,%d,%d,%s>", block, unroll, warps, fast ? "true" : "false");
+    }
+    const char *xchg = h->world == 1 ? "one GPU, no exchange"
+                     : h->exchange == HGB_EXCHANGE_P2P ? "targets sharded, results stored into every peer's next state over NVLink (fused epilogue)"
+                                                       : "targets sharded, ncclAllGather of positions per step";
+    snprintf(buf, (size_t)capacity, "%s | %s", kern, xchg);
+    return HGB_OK;
+}
+
+double hgb_nbody_fp64_instr(const hgb_nbody *h) {
+    if (!h) return 0.0;
+    if (h->mode == HGB_NBODY_FAST) return 16.0;    // FMA-contracted rsqrt-Newton sequence
+    return sym_applies(h) ? 16.0 : 29.0;           // 32 per PAIR (26 + 3 + 3) vs 17 + 8 + 4 per interaction
+}
+
 int hgb_nbody_sym_counters(hgb_nbody *h, unsigned long long *out7) {
     HGB_ARG(h && out7, "handle / out");
     NbShard &s = h->sh[0];

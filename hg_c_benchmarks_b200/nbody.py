@@ -70,6 +70,13 @@ class NBody:
         check(lib().hgb_nbody_set_symmetric(self._h, int(variant), int(min_n)))
         return self
 
+    def describe(self):
+        """(kernel, parallelism) the next step() will use on this handle as configured now"""
+        buf = C.create_string_buffer(512)
+        check(lib().hgb_nbody_describe(self._h, buf, 512))
+        kernel, _, par = buf.value.decode().partition(" | ")
+        return kernel, par
+
     def upload(self, pos):
         _bodies(pos, "pos")
         assert pos.shape[0] == self.n

@@ -100,6 +100,12 @@ int hgb_nbody_tune(hgb_nbody *h, int block, int unroll, int warps);
 int hgb_nbody_set_symmetric(hgb_nbody *h, int variant, int min_n);
 /* the variant hgb_nbody_step will use on this handle as configured now (0: the standard kernel) */
 int hgb_nbody_symmetric(const hgb_nbody *h);
+/* "<kernel> | <how targets/pairs are spread over the GPUs>" of the next hgb_nbody_step on this handle
+ * as configured now (bench.py's config.kernel / config.parallelism) */
+int hgb_nbody_describe(const hgb_nbody *h, char *buf, int capacity);
+/* FP64-pipe instructions that kernel issues per interaction (SASS count, tools/sass_loop.py):
+ * the numerator of the pipe-utilisation figure bench.py reports */
+double hgb_nbody_fp64_instr(const hgb_nbody *h);
 /* diagnostics: clock64 spans summed over all warps of the last step run with a profiling variant
  * (1226, 1242): tag wait, chunk loads, chunk release, predicate-free loop, predicated steps, whole
  * workers, chunks opened */

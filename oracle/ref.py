@@ -23,19 +23,40 @@ _VARIANT = ""
 def build(reference="/root/reference", pgo=True):
     if not os.path.isdir(reference):
         raise RuntimeError("reference sources not present; oracle/_ref cannot be (re)built here")
-    subprocess.run(["make", "-C", _HERE, "ref"] + (["ref-pgo"] if pgo else []) + [f"REF={reference}"],
+    subprocess.run(["make", "-C", _HERE, "ref", "ref-v4"] + (["ref-pgo"] if pgo else []) + [f"REF={reference}"],
                    check=True, capture_output=True)
 
 
+def _cpu_has_avx512():
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("flags"):
+                    flags = set(line.split(":", 1)[1].split())
+                    return {"avx512f", "avx512bw", "avx512cd", "avx512dq", "avx512vl"} <= flags
+    except OSError:
+        pass
+    return False
+
+
 def available(variant=""):
+    """variant "" (x86-64-v3, shipped -O2/-O3), "_pgo" (-O3 + profile feedback) or "_v4" (AVX-512: what
+    the reference's -march=native gives on such a host; only offered when the CPU can run it)"""
+    if variant == "_v4" and not _cpu_has_avx512():
+        return False
     return (os.path.exists(os.path.join(_REF, f"libhgref_nbody{variant}.so"))
             and os.path.exists(os.path.join(_REF, f"libhgref_conv{variant}.so")))
 
 
+VARIANTS = {"": "shipped flags, -march=x86-64-v3 (-std=c11 -O2 nbody / -O3 convolution, -fopenmp)",
+            "_pgo": "-O3 + gcc profile feedback (pgo.sh's intent), -march=x86-64-v3",
+            "_v4": "shipped flags, -march=x86-64-v4 (AVX-512: the reference's -march=native on this host)"}
+
+
 def use(variant=""):
-    """select which build of the unmodified reference the functions below call: "" or "_pgo" """
+    """select which build of the unmodified reference the functions below call"""
     global _VARIANT
-    assert variant in ("", "_pgo") and available(variant), variant
+    assert variant in VARIANTS and available(variant), variant
     _VARIANT = variant
 
 

@@ -278,11 +278,15 @@ def test_row_bands_over_gpus_are_bit_identical(hgb, monkeypatch, exchange, depth
     counts = _gpu_counts(hgb, monkeypatch, exchange)
     p = k // 2
     kind = hgb.EXCHANGE_NCCL if exchange == "nccl" else hgb.EXCHANGE_P2P
+    from oracle import port
     img = synth.add_padding(synth.image_float(w, h, seed=w), p)
     with hgb.convolution.Conv2D(w, h, p, ngpus=1) as one:
         one.set_kernel(synth.kernel_dense(k)).upload(img)
         one.step(it)
         want_c, want_p = one.download(want_prev=True)
+    o_c, o_p = img.copy(), np.zeros_like(img)                 # the oracle, not only the 1-GPU result
+    port.conv_run(o_c, o_p, w, h, p, synth.kernel_dense(k), it)
+    assert np.array_equal(want_c, o_c) and np.array_equal(want_p, o_p)
     for gg in counts:
         with hgb.convolution.Conv2D(w, h, p, ngpus=gg) as cv:
             cv.set_exchange(kind).set_kernel(synth.kernel_dense(k)).upload(img)

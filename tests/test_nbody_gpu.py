@@ -222,17 +222,63 @@ def test_target_sharding_over_gpus_is_bit_identical(hgb, monkeypatch, exchange, 
         monkeypatch.setenv("HGB_VIRTUAL_GPUS", "4")
         g = 4
     kind = hgb.EXCHANGE_NCCL if exchange == "nccl" else hgb.EXCHANGE_P2P
+    from oracle import port
     pos = synth.plummer(n, seed=n)
     with hgb.nbody.NBody(n, ngpus=1) as one:
         one.upload(pos)
         one.step(iters)
         want_cur, want_prev = one.download(want_prev=True)
+    # the oracle, not only the 1-GPU result: whole run for the small sets, a target sample of the
+    # last step for the large one
+    if n <= 5000:
+        a, b = pos.copy(), np.zeros_like(pos)
+        port.nbody_run(a, b, iters)
+        o_cur, o_prev = (a, b) if iters % 2 == 0 else (b, a)
+        assert np.array_equal(want_cur, o_cur) and np.array_equal(want_prev, o_prev)
+    sample = np.random.default_rng(n).choice(n, size=min(n, 96), replace=False).astype(np.int32)
     for gg in sorted({2, g}):
         with hgb.nbody.NBody(n, ngpus=gg, exchange=kind) as nb:
             nb.upload(pos)
             nb.step(iters)
             cur, prev = nb.download(want_prev=True)
         assert np.array_equal(cur, want_cur) and np.array_equal(prev, want_prev), (exchange, gg)
+        assert np.array_equal(cur[sample], port.nbody_accel_subset(prev, sample)), (exchange, gg)
+
+
+def test_a_live_handle_survives_the_creation_of_a_wider_one(hgb, monkeypatch):
+    """device contexts must not move when a handle over more GPUs is created (a 1-GPU handle keeps
+    pointers to its stream and events): step the old handle after the new one exists, and again
+    after the new one is gone; same for the cached drop-in handles."""
+    from oracle import port
+    monkeypatch.setenv("HGB_VIRTUAL_GPUS", "4")
+    n = 1500
+    pos = synth.plummer(n, seed=5)
+    want = np.zeros_like(pos)
+    port.nbody_step_range(pos, want, 0, n)
+    one = hgb.nbody.NBody(n, ngpus=1)
+    one.upload(pos)
+    one.step(1)
+    assert np.array_equal(one.download(), want)
+    wide = hgb.nbody.NBody(n, ngpus=4, exchange=hgb.EXCHANGE_P2P)
+    wide.upload(pos)
+    wide.step(1)
+    assert np.array_equal(wide.download(), want)
+    one.upload(pos)
+    one.step(1)                                   # contexts of devices 0..3 were added behind it
+    assert np.array_equal(one.download(), want)
+    wide.close()
+    one.upload(pos)
+    one.step(1)
+    assert np.array_equal(one.download(), want)
+    one.close()
+    for g in (1, 4, 1):                           # drop-in: cached handles of different widths in turn
+        a, b = pos.copy(), np.zeros_like(pos)
+        hgb.nbody.set_exchange(hgb.EXCHANGE_P2P)
+        try:
+            hgb.nbody.run(a, b, n, 1, g)
+        finally:
+            hgb.nbody.set_exchange(hgb.EXCHANGE_NCCL)
+        assert np.array_equal(b, want), g
 
 
 def test_drop_in_with_number_of_processes_as_gpu_count(hgb):
