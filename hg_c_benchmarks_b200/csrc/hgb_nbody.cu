@@ -56,18 +56,15 @@ static void launch_variant(bool fast, int grid, cudaStream_t st, const double *s
                                                                              tlist, out, out_list, none, run_if);
 }
 
-// CTA shape for `count` targets when the caller did not pin one (hgb_nbody_tune).  Large counts:
-// 128-thread CTAs, 6 per SM (measured best at N = 2^20, profiles/r1_nbody_sweep.txt).  When the grid is
-// below one wave the step lasts as long as the SM with the most targets, ceil(CTAs / SMs) * block of
-// them against count / SMs on average: 64-thread CTAs cut that rounding loss (N = 65536 on 148 SMs:
-// 4 x 128 = 512 targets on the fullest SM vs 7 x 64 = 448, average 443).
+// CTA shape for `count` targets when the caller did not pin one (hgb_nbody_tune): 128-thread CTAs, 6 per
+// SM, two double2 source loads per group (measured best at N = 2^20, profiles/r1_nbody_sweep.txt).  Below
+// one wave (N = 65536: 3.46 CTAs per SM) the kernel runs at ~80 % of its large-N rate; that is a latency
+// effect of ~14 warps per SM, not the rounding of CTAs over SMs: 64-thread CTAs (7 x 64 = 448 targets on
+// the fullest SM instead of 4 x 128 = 512) measure the same or slower (profiles/r2a_nbody_small_sweep.txt:
+// 9.69 ms for 128/2/24, 9.71 ms for 64/2/24, 10.29 ms for 64/2/28), so the shape stays fixed.
 static void auto_shape(int count, int sms, int *block, int *unroll, int *warps) {
+    (void)count; (void)sms;
     *block = 128; *unroll = 2; *warps = 24;
-    if (sms <= 0) return;
-    const long ctas128 = (count + 127) / 128, ctas64 = (count + 63) / 64;
-    if (ctas128 >= 6L * sms) return;                         // a full wave or more
-    const long worst128 = (ctas128 + sms - 1) / sms * 128, worst64 = (ctas64 + sms - 1) / sms * 64;
-    if (worst64 < worst128 && ctas64 <= 14L * sms) { *block = 64; *warps = 28; }
 }
 
 static int launch_step(const hgb_nbody *h, const NbShard &s, const double *src, int t0, int count,

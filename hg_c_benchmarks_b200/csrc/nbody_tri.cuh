@@ -1,0 +1,373 @@
+// nbody_tri.cuh -- pair-symmetric all-pairs FP64 step for sm_100a, second generation: the force of
+// every unordered pair is evaluated once (EXACT mode, bit-identical to accel(), reference
+// src/nbody/nbody-run.c:17-25) and the ORDERED accumulation is decoupled from the force evaluation,
+// so the wavefront's critical path carries 3 adds per pair instead of the whole 32-instruction
+// chain, rows can be cut into segments (no long tail), and the work can be dealt over several GPUs.
+//
+// Pair (i, j), j < i, contributes v = d * f (pair_wise_accel, reference src/nbody/nbody-run.c:6-15,
+// evaluated from target i's side) to acc_i at position j of i's sum and -v to acc_j at position i of
+// j's sum -- bit for bit what the reference adds there (d(j->i) = -d(i->j) exactly, same s, t, f).
+//
+//   * ROW I = the 32 targets 32I .. 32I+31, one per lane of a warp, position and accumulator in
+//     registers.  Its lower sources j < 32I are cut into SEGMENTS of `seg` sources; ITEM (I, k) =
+//     row I against segment k (the last item of a row also does the row's own 32 x 32 triangle).
+//     An item is the unit of scheduling: a warp takes a ticket, runs one item, takes the next ticket.
+//   * MINITILE = 32 targets x 8 consecutive sources.  Each lane evaluates its 8 pairs (8 interleaved
+//     dependency chains, 208 FP64 instructions per warp), adds them to its own accumulator in source
+//     order (ROW pass: 24 instructions), and writes the 8 x 3 values into a shared-memory transposed
+//     buffer.  COLUMN pass: lane L < 24 owns (component L / 8, source L % 8) of the minitile, takes
+//     that source's running sum ("chain": the accumulator of body j as a TARGET, which has already
+//     absorbed every target below this row), subtracts the 32 targets' values in target order (32
+//     dependent instructions with 24 of 32 lanes busy: 264 instead of the ideal 256 per minitile)
+//     and publishes the result for the next row.  The column pass of minitile m is issued INSIDE the
+//     force evaluation of minitile m+1 (one basic block, independent instruction streams), so its
+//     latency hides under the throughput-bound part.
+//   * Hand-off between rows: tagged words (payload + tag in every 8-byte half: one 16-byte store
+//     publishes value and flag, no fence; the "LL" scheme of collective libraries).  Row I expects
+//     tag (epoch | I), written by row I-1, and publishes with (epoch | I+1) -- into the local buffer,
+//     or into the buffer of the GPU that runs row I+1 (peer-mapped pointer: the store crosses NVLink).
+//     The last row publishes into EVERY GPU's buffer: those words are the finished accumulators, so
+//     no position exchange follows the step.
+//   * Hand-off between the items of one row: the row's 32 x 3 accumulators through a tagged buffer.
+//   * Order.  Items are grouped in TILES (b, k) = the `tr` = seg/32 rows of super-row b against segment
+//     k, k <= b.  Item (I, k) needs (I, k-1) finished (row accumulators) and streams the chain words of
+//     (I-1, k) minitile by minitile; the host lists the tiles of each GPU in anti-diagonal order
+//     (b + k ascending), a linear extension of those dependencies, and warps take tickets in that
+//     order, so a warp only ever waits for an item with an earlier ticket, which a resident warp is
+//     already running (persistent grid, no deadlock); super-row b lives on GPU b mod g.
+// tests/tri_model.py is a CPU model of exactly this index logic.
+#pragma once
+#include "nbody_sym.cuh"
+
+namespace hgb {
+
+constexpr int kTriWarps = 4;          // warps (independent workers) per CTA
+constexpr int kTriCtlInts = 32;       // ctl[0] ticket, ctl[1] range flag, ctl[2] abort flag, ctl[8..] profiling
+constexpr int kTbPitch = 34;          // doubles per row of the transposed buffer (16-byte rows, conflict-free LDS.128)
+constexpr int kTriWarpDoubles = 2 * 3 * 32 + 2 * 24 * kTbPitch + 32;   // ring + 2 transposed buffers + chain seeds
+constexpr size_t kTriSmem = (size_t)kTriWarps * kTriWarpDoubles * sizeof(double);
+
+struct TriArgs {
+    const double *src;        // SoA positions, component stride npad, zero beyond n
+    int npad, n;
+    int T;                    // rows = ceil(n / 32)
+    int seg, tr;              // sources per segment (multiple of 32), rows per tile = seg / 32
+    const int2 *tiles;        // this GPU's tiles (b, k) in ticket order
+    int ntiles;
+    ulonglong2 *ll;           // chain words this GPU reads: [chunk of 32 sources][x, y, z][32] x 16 B
+    ulonglong2 *ll_down;      // where the LAST row of a super-row publishes (buffer of the next super-row's GPU)
+    ulonglong2 *ll_all[kMaxPeers];   // every GPU's buffer: the last row of the step publishes into all of them
+    int npeers;
+    ulonglong2 *racc;         // row accumulators between the items of a row: [row][x, y, z][32] x 16 B
+    unsigned epoch_tag;       // (launch epoch) << 21
+    int *ctl;
+    int *ctl_all[kMaxPeers];  // peers' ctl (range / abort flags are raised everywhere)
+    long long spin_limit;     // clock64 ticks a poll may last before the step is abandoned
+};
+
+// d * f of pair_wise_accel for one target against 8 sources, fused with the COLUMN pass of the
+// previous minitile: `col` points at this lane's row of that minitile's transposed buffer (32 values,
+// target order) and `chain` is the running sum they are subtracted from.  One basic block: ptxas
+// interleaves the dependent chain (LDS -> DSUB -> DSUB ...) with the eight independent force chains.
+template <bool ALLV>
+__device__ __forceinline__ void forces_and_column(double px, double py, double pz, const double (&xj)[8],
+                                                  const double (&yj)[8], const double (&zj)[8],
+                                                  double (&vx)[8], double (&vy)[8], double (&vz)[8],
+                                                  unsigned &key, const double *col, double &chain, int cnt) {
+    constexpr int P = 8;
+    double t[P], y[P], g[P], s[P], a[P], e[P], p[P], q[P];
+    int ct = 0;   // column pairs consumed so far (compile-time after unrolling)
+    auto column = [&](int pairs) {
+#pragma unroll
+        for (int w = 0; w < pairs; ++w, ++ct) {
+            const double2 v = *reinterpret_cast<const double2 *>(col + 2 * ct);
+            if (ALLV || 2 * ct < cnt) chain = __dsub_rn(chain, v.x);
+            if (ALLV || 2 * ct + 1 < cnt) chain = __dsub_rn(chain, v.y);
+        }
+    };
+#pragma unroll
+    for (int u = 0; u < P; ++u) { vx[u] = __dsub_rn(xj[u], px); vy[u] = __dsub_rn(yj[u], py); vz[u] = __dsub_rn(zj[u], pz); }
+    column(2);
+#pragma unroll
+    for (int u = 0; u < P; ++u) { s[u] = __dmul_rn(vx[u], vx[u]); a[u] = __dmul_rn(vy[u], vy[u]); e[u] = __dmul_rn(vz[u], vz[u]); }
+    column(2);
+#pragma unroll
+    for (int u = 0; u < P; ++u) s[u] = __dadd_rn(s[u], a[u]);
+    column(1);
+#pragma unroll
+    for (int u = 0; u < P; ++u) s[u] = __dadd_rn(s[u], e[u]);
+    column(1);
+#pragma unroll
+    for (int u = 0; u < P; ++u) s[u] = __dadd_rn(s[u], kEps);
+    column(1);
+#pragma unroll
+    for (int u = 0; u < P; ++u) t[u] = __dmul_rn(s[u], s[u]);
+    column(1);
+#pragma unroll
+    for (int u = 0; u < P; ++u) t[u] = __dmul_rn(t[u], s[u]);            // (s*s)*s
+    column(1);
+#pragma unroll
+    for (int u = 0; u < P; ++u) { y[u] = mufu_rsqrt(t[u]); key = max(key, range_key(t[u])); }
+#pragma unroll
+    for (int u = 0; u < P; ++u) a[u] = __dmul_rn(y[u], y[u]);
+    column(1);
+#pragma unroll
+    for (int u = 0; u < P; ++u) e[u] = __fma_rn(t[u], -a[u], 1.0);
+    column(1);
+#pragma unroll
+    for (int u = 0; u < P; ++u) { p[u] = __fma_rn(e[u], 0.375, 0.5); q[u] = __dmul_rn(y[u], e[u]); }
+    column(1);
+#pragma unroll
+    for (int u = 0; u < P; ++u) y[u] = __fma_rn(p[u], q[u], y[u]);       // ~1/sqrt(t)
+    column(1);
+#pragma unroll
+    for (int u = 0; u < P; ++u) g[u] = __dmul_rn(t[u], y[u]);
+    column(1);
+#pragma unroll
+    for (int u = 0; u < P; ++u) e[u] = __fma_rn(-g[u], g[u], t[u]);
+    column(1);
+#pragma unroll
+    for (int u = 0; u < P; ++u) g[u] = __fma_rn(e[u], half_of(y[u]), g[u]);  // RN(sqrt(t))
+    column(1);
+#pragma unroll
+    for (int u = 0; u < P; ++u) y[u] = odd_up(y[u]);                     // see inv_sqrt_ieee
+#pragma unroll
+    for (int u = 0; u < P; ++u) e[u] = __fma_rn(y[u], -g[u], 1.0);
+#pragma unroll
+    for (int u = 0; u < P; ++u) y[u] = __fma_rn(y[u], e[u], y[u]);
+#pragma unroll
+    for (int u = 0; u < P; ++u) e[u] = __fma_rn(y[u], -g[u], 1.0);
+#pragma unroll
+    for (int u = 0; u < P; ++u) y[u] = __fma_rn(y[u], e[u], y[u]);       // RN(1/g)
+#pragma unroll
+    for (int u = 0; u < P; ++u) { vx[u] = __dmul_rn(vx[u], y[u]); vy[u] = __dmul_rn(vy[u], y[u]); vz[u] = __dmul_rn(vz[u], y[u]); }
+    static_assert(2 + 2 + 12 == 16, "16 column pairs = 32 targets");
+}
+
+// CTAS resident CTAs per SM (register budget).  PROF: lane 0 of every warp accumulates clock64 spans
+// (waits for chain words, waits for row accumulators, whole items, the diagonal triangles) in ctl[8..].
+template <int CTAS, bool PROF = false>
+__global__ void __launch_bounds__(kTriWarps * 32, CTAS)
+nbody_tri_kernel(const __grid_constant__ TriArgs a) {
+    constexpr unsigned FULL = 0xffffffffu;
+    extern __shared__ __align__(16) double tri_smem[];
+    const int lane = threadIdx.x & 31;
+    double *ring = tri_smem + (threadIdx.x >> 5) * kTriWarpDoubles;   // [slot 2][comp 3][32]
+    double *tb = ring + 2 * 3 * 32;                                   // [buffer 2][24][kTbPitch]
+    double *seed = tb + 2 * 24 * kTbPitch;                            // [24] chain seeds of a diagonal minitile
+    const double *sx = a.src, *sy = a.src + a.npad, *sz = a.src + 2 * (size_t)a.npad;
+    const int col_lane = lane < 24 ? lane : 23;                       // lanes 24..31 shadow lane 23 and never publish
+    const int cc = col_lane >> 3, cu = col_lane & 7;                  // component, source within the minitile
+    unsigned key = 0;
+    bool dead = false;                                                // the step was abandoned (spin limit)
+    long long t_chain = 0, t_racc = 0, t_item = 0, t_diag = 0, n_items = 0;
+    auto now = [] { return PROF ? clock64() : 0ll; };
+
+    // a poll that has lasted too long raises the abort flag everywhere; everyone then runs to the end
+    // without waiting (results are garbage, the host reports the failure)
+    auto give_up = [&](long long t0) -> bool {
+        if (dead) return true;
+        if (*reinterpret_cast<volatile int *>(a.ctl + 2) != 0) { dead = true; return true; }
+        if (clock64() - t0 > a.spin_limit) {
+            for (int p = 0; p < a.npeers; ++p) *reinterpret_cast<volatile int *>(a.ctl_all[p] + 2) = 1;
+            dead = true;
+            return true;
+        }
+        return false;
+    };
+
+    for (;;) {
+        int ticket = 0;
+        if (lane == 0) ticket = atomicAdd(&a.ctl[0], 1);
+        ticket = __shfl_sync(FULL, ticket, 0);
+        const int ti = ticket / a.tr, r = ticket - ti * a.tr;
+        if (ti >= a.ntiles) break;
+        const int2 bk = a.tiles[ti];
+        const int I = bk.x * a.tr + r, k = bk.y;
+        if (I >= a.T) continue;
+        const long long it0 = now();
+        const int i0 = 32 * I;
+        const bool last_item = k == bk.x;                 // floor(32 I / seg) == b: this item ends the row
+        const int j_begin = k * a.seg, j_end = last_item ? i0 : (k + 1) * a.seg;
+        const int cnt = min(32, a.n - i0);                // valid targets of the row (32 except in the last row)
+        const bool final_row = I == a.T - 1;
+        const unsigned want_tag = a.epoch_tag | (unsigned)I;          // written by row I-1
+        const unsigned my_tag = a.epoch_tag | (unsigned)(I + 1);
+        ulonglong2 *pub = (r == a.tr - 1) ? a.ll_down : a.ll;         // row I+1 is the next super-row's first row
+
+        const double px = sx[i0 + lane], py = sy[i0 + lane], pz = sz[i0 + lane];
+        double ax = 0.0, ay = 0.0, az = 0.0;
+        if (k > 0) {   // the row's sums so far, left by item (I, k-1)
+            const ulonglong2 *q = a.racc + (size_t)I * 96 + lane;
+            const unsigned tag = a.epoch_tag | (unsigned)k;
+            const long long w0 = clock64();
+            ulonglong2 wx = ll_load(q), wy = ll_load(q + 32), wz = ll_load(q + 64);
+            while (!__all_sync(FULL, ll_ok(wx, tag) && ll_ok(wy, tag) && ll_ok(wz, tag))) {
+                if (give_up(w0)) break;
+                __nanosleep(100);
+                wx = ll_load(q); wy = ll_load(q + 32); wz = ll_load(q + 64);
+            }
+            ax = ll_unpack(wx); ay = ll_unpack(wy); az = ll_unpack(wz);
+            if (PROF) t_racc += clock64() - w0;
+        }
+
+        // chain word of (minitile mt of chunk ch) for this column lane
+        auto word_index = [&](int chunk, int mt) { return (size_t)chunk * 96 + cc * 32 + mt * 8 + cu; };
+        auto publish = [&](int chunk, int mt, double chain) {
+            if (lane >= 24) return;
+            const ulonglong2 w = ll_pack(chain, my_tag);
+            const size_t at = word_index(chunk, mt);
+            if (final_row) {
+                for (int p = 0; p < a.npeers; ++p) ll_store(a.ll_all[p] + at, w);
+            } else {
+                ll_store(pub + at, w);
+            }
+        };
+        auto wait_word = [&](ulonglong2 &w, int chunk, int mt) -> double {
+            if (!__all_sync(FULL, ll_ok(w, want_tag))) {
+                const long long w0 = clock64();
+                const ulonglong2 *q = a.ll + word_index(chunk, mt);
+                do {
+                    if (give_up(w0)) break;
+                    __nanosleep(40);
+                    w = ll_load(q);
+                } while (!__all_sync(FULL, ll_ok(w, want_tag)));
+                if (PROF) t_chain += clock64() - w0;
+            }
+            return ll_unpack(w);
+        };
+
+        auto lower = [&](auto allv) {
+            constexpr bool ALLV = decltype(allv)::value;
+            const int chunk0 = j_begin >> 5, nchunks = (j_end - j_begin) >> 5;
+            if (nchunks <= 0) return;
+            double fx = sx[j_begin + lane], fy = sy[j_begin + lane], fz = sz[j_begin + lane];   // next chunk's positions
+            ulonglong2 cw[4];                                                                 // chain words in flight
+#pragma unroll
+            for (int q = 0; q < 4; ++q) cw[q] = ll_load(a.ll + word_index(chunk0, q));
+            double chain = 0.0;
+#pragma unroll 1
+            for (int ch = 0; ch < nchunks; ++ch) {
+                double *slot = ring + (ch & 1) * 96;
+                slot[lane] = fx; slot[32 + lane] = fy; slot[64 + lane] = fz;
+                __syncwarp();
+                if (ch + 1 < nchunks) {
+                    const int g = j_begin + 32 * (ch + 1) + lane;
+                    fx = sx[g]; fy = sy[g]; fz = sz[g];
+                }
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    // minitile (ch, q): forces + row pass; column pass of the minitile before it
+                    const bool have_prev = ch > 0 || q > 0;
+                    const int pch = q > 0 ? ch : ch - 1, pq = (q + 3) & 3;       // the previous minitile
+                    if (have_prev) {
+                        chain = wait_word(cw[pq], chunk0 + pch, pq);
+                        if (pch + 1 < nchunks) cw[pq] = ll_load(a.ll + word_index(chunk0 + pch + 1, pq));   // four minitiles ahead
+                    }
+                    double xj[8], yj[8], zj[8], vx[8], vy[8], vz[8];
+#pragma unroll
+                    for (int u = 0; u < 8; u += 2) {
+                        const double2 x2 = *reinterpret_cast<const double2 *>(slot + q * 8 + u);
+                        const double2 y2 = *reinterpret_cast<const double2 *>(slot + 32 + q * 8 + u);
+                        const double2 z2 = *reinterpret_cast<const double2 *>(slot + 64 + q * 8 + u);
+                        xj[u] = x2.x; xj[u + 1] = x2.y; yj[u] = y2.x; yj[u + 1] = y2.y; zj[u] = z2.x; zj[u + 1] = z2.y;
+                    }
+                    const double *col = tb + ((q + 1) & 1) * 24 * kTbPitch + col_lane * kTbPitch;   // buffer of minitile (ch,q)-1
+                    forces_and_column<ALLV>(px, py, pz, xj, yj, zj, vx, vy, vz, key, col, chain, cnt);
+                    if (have_prev) publish(chunk0 + pch, pq, chain);
+                    double *mine = tb + (q & 1) * 24 * kTbPitch + lane;
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {   // row pass: sources ascending, the target's order
+                        ax = __dadd_rn(ax, vx[u]); ay = __dadd_rn(ay, vy[u]); az = __dadd_rn(az, vz[u]);
+                        mine[u * kTbPitch] = vx[u]; mine[(8 + u) * kTbPitch] = vy[u]; mine[(16 + u) * kTbPitch] = vz[u];
+                    }
+                    __syncwarp();   // column lanes read these values during the next minitile
+                }
+            }
+            // column pass of the segment's last minitile (chunk nchunks-1, minitile 3: buffer 1)
+            chain = wait_word(cw[3], chunk0 + nchunks - 1, 3);
+            const double *col = tb + 24 * kTbPitch + col_lane * kTbPitch;
+#pragma unroll
+            for (int tcol = 0; tcol < 16; ++tcol) {
+                const double2 v = *reinterpret_cast<const double2 *>(col + 2 * tcol);
+                if (ALLV || 2 * tcol < cnt) chain = __dsub_rn(chain, v.x);
+                if (ALLV || 2 * tcol + 1 < cnt) chain = __dsub_rn(chain, v.y);
+            }
+            publish(chunk0 + nchunks - 1, 3, chain);
+            __syncwarp();
+        };
+        if (cnt == 32) lower(std::true_type{});
+        else lower(std::false_type{});
+
+        if (!last_item) {   // hand the row's sums to item (I, k+1)
+            ulonglong2 *q = a.racc + (size_t)I * 96 + lane;
+            const unsigned tag = a.epoch_tag | (unsigned)(k + 1);
+            ll_store(q, ll_pack(ax, tag)); ll_store(q + 32, ll_pack(ay, tag)); ll_store(q + 64, ll_pack(az, tag));
+        } else {
+            // the row's own 32 x 32 triangle: sources j = i0 + 8 mt + u against targets i > j.  The sources are
+            // the warp's own targets (positions by shuffle).  After the row pass of minitile mt the lanes
+            // 8 mt .. 8 mt + 7 hold their complete lower sums: those seed the chains of the minitile's sources.
+            const long long d0 = now();
+#pragma unroll 1
+            for (int mt = 0; mt < 4; ++mt) {
+                double qx[8], qy[8], qz[8], jx[8], jy[8], jz[8], vx[8], vy[8], vz[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    jx[u] = __shfl_sync(FULL, px, mt * 8 + u); jy[u] = __shfl_sync(FULL, py, mt * 8 + u);
+                    jz[u] = __shfl_sync(FULL, pz, mt * 8 + u);
+                    qx[u] = px; qy[u] = py; qz[u] = pz;
+                }
+                pair_forces<8>(qx, qy, qz, jx, jy, jz, vx, vy, vz, key);
+                double *mine = tb + lane;
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    if (mt * 8 + u < lane) {   // j < i
+                        ax = __dadd_rn(ax, vx[u]); ay = __dadd_rn(ay, vy[u]); az = __dadd_rn(az, vz[u]);
+                    }
+                    mine[u * kTbPitch] = vx[u]; mine[(8 + u) * kTbPitch] = vy[u]; mine[(16 + u) * kTbPitch] = vz[u];
+                }
+                if ((lane >> 3) == mt) { seed[lane & 7] = ax; seed[8 + (lane & 7)] = ay; seed[16 + (lane & 7)] = az; }
+                __syncwarp();
+                double chain = seed[col_lane];
+                const double *col = tb + col_lane * kTbPitch;
+                for (int i = mt * 8 + cu + 1; i < cnt; ++i) chain = __dsub_rn(chain, col[i]);
+                publish(I, mt, chain);
+                __syncwarp();
+            }
+            if (PROF) t_diag += now() - d0;
+        }
+        if (PROF) { t_item += now() - it0; ++n_items; }
+    }
+    if (PROF && lane == 0) {
+        unsigned long long *c = reinterpret_cast<unsigned long long *>(a.ctl + 8);
+        atomicAdd(c + 0, (unsigned long long)t_chain); atomicAdd(c + 1, (unsigned long long)t_racc);
+        atomicAdd(c + 2, (unsigned long long)t_item); atomicAdd(c + 3, (unsigned long long)t_diag);
+        atomicAdd(c + 4, (unsigned long long)n_items);
+    }
+    if (key >= kRangeLimit)
+        for (int p = 0; p < a.npeers; ++p) *reinterpret_cast<volatile int *>(a.ctl_all[p] + 1) = 1;
+}
+
+// buffer[i] = G * acc[i] (reference src/nbody/nbody-run.c:22-24).  acc = what the LAST row published (tag
+// epoch | T) into this GPU's buffer -- possibly from another GPU, whose kernel may still be running, so
+// the words are polled; a poll that outlasts the spin limit raises the abort flag.
+__global__ void __launch_bounds__(256)
+nbody_tri_finish_kernel(const ulonglong2 *__restrict__ ll, int npad, int n, unsigned final_tag, double *out,
+                        int *ctl, long long spin_limit) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const ulonglong2 *q = ll + (size_t)(i >> 5) * 96 + (i & 31);
+    ulonglong2 wx = ll_load(q), wy = ll_load(q + 32), wz = ll_load(q + 64);
+    const long long t0 = clock64();
+    while (!(ll_ok(wx, final_tag) && ll_ok(wy, final_tag) && ll_ok(wz, final_tag))) {
+        if (*reinterpret_cast<volatile int *>(ctl + 2) != 0) break;
+        if (clock64() - t0 > spin_limit) { *reinterpret_cast<volatile int *>(ctl + 2) = 1; break; }
+        __nanosleep(200);
+        wx = ll_load(q); wy = ll_load(q + 32); wz = ll_load(q + 64);
+    }
+    out[i] = __dmul_rn(kG, ll_unpack(wx));
+    out[(size_t)npad + i] = __dmul_rn(kG, ll_unpack(wy));
+    out[2 * (size_t)npad + i] = __dmul_rn(kG, ll_unpack(wz));
+}
+
+}  // namespace hgb

@@ -85,8 +85,7 @@ int hgb_nbody_create(hgb_nbody **out, int n, int ngpus);
 /* one process per GPU: this rank owns target shard hgb_comm_rank() of hgb_comm_world() */
 int hgb_nbody_create_rank(hgb_nbody **out, int n);
 int hgb_nbody_config(hgb_nbody *h, int mode, int exchange);
-/* kernel variant; 0 = automatic (128-thread CTAs, 6 per SM; 64-thread CTAs when the target count is
- * below one wave and they balance better over the SMs): threads per CTA {64,128,256}, sources per
+/* kernel variant; 0 = default (128-thread CTAs, 6 per SM, unroll 2): threads per CTA {64,128,256}, sources per
  * unrolled group/2 {1,2,4}, resident warps per SM the register allocation allows {24,28,32,40}
  * (28: 64/128-thread CTAs; 64-thread CTAs: (unroll, warps) in {(2,28), (2,24), (4,24), (1,28)}) */
 int hgb_nbody_tune(hgb_nbody *h, int block, int unroll, int warps);

@@ -88,7 +88,7 @@ def test_every_kernel_variant_gives_the_same_bits(hgb):
             nb.tune(block, unroll, warps).upload(pos)
             nb.step(1)
             assert np.array_equal(nb.download(), want), (block, unroll, warps)
-    # the automatic shape (64-thread CTAs below one wave) on ragged counts around the tile sizes
+    # ragged counts around the tile sizes
     for m in (1, 63, 64, 65, 255, 257, 511, 513, 2999):
         sub = np.ascontiguousarray(pos[:m])
         w2 = np.zeros_like(sub)
