@@ -4,6 +4,7 @@
 #include "hgb_common.cuh"
 #include "nbody_kernels.cuh"
 #include "nbody_sym.cuh"
+#include "nbody_tri.cuh"
 
 using namespace hgb;
 
@@ -23,6 +24,12 @@ struct NbShard {
     int *sym_ctl = nullptr;      // pair-symmetric kernel: ticket, range flag, profiling counters (nbody_sym.cuh)
     ulonglong2 *sym_ll = nullptr; // ... tagged chain accumulators, 48 B per body
     unsigned sym_epoch = 0;
+    // second-generation pair-symmetric kernel (nbody_tri.cuh)
+    int *tri_ctl = nullptr;                       // ticket, range flag, abort flag, profiling counters
+    ulonglong2 *tri_ll[2] = {nullptr, nullptr};   // chain words, double-buffered by step parity, 48 B per body each
+    ulonglong2 *tri_racc = nullptr;               // row accumulators between the items of a row, 48 B per body
+    int2 *tri_tiles = nullptr;                    // this shard's tiles in ticket order
+    int tri_ntiles = 0, tri_plan_seg = 0;
 };
 }  // namespace
 
@@ -36,6 +43,9 @@ struct hgb_nbody {
     bool dynamics = false;  // hgb_nbody_set_dynamics was called
     int sym = 0;            // pair-symmetric kernel variant R*100 + U*10 + CTAs/SM (0 = off)
     int sym_min_n = 0;      // ... used when n >= sym_min_n, one GPU, EXACT mode
+    int tri_seg = 0;        // second-generation kernel (variants 2000+): sources per segment
+    unsigned tri_step = 0;  // steps run with it so far (epoch and buffer parity)
+    int tri_status = 0;     // abort flag read back after the last advance
     double dt = 0.0;
     std::vector<NbShard> sh;
 };
@@ -101,7 +111,10 @@ static int g_default_sym = -1, g_default_sym_min_n = -1;   // -1: read HGB_NBODY
 constexpr int kSymDefaultVariant = 242;                    // R = 2, U = 4, 2 CTAs (8 warps) per SM: profiles/r1e_nbody_sym_sweep_*.txt
 constexpr int kSymDefaultMinN = 393216;                    // measured: slower than the standard kernel at 2^18, 26 % faster at 2^19
 
+static bool tri_variant(int v) { return v >= 2001 && v <= 2013 && (v % 10) >= 1 && (v % 10) <= 3; }   // 200C / 201C (profiling)
+
 static bool sym_variant_known(int v) {
+    if (tri_variant(v)) return true;
     switch (v) {
         case 124: case 146: case 148: case 224: case 226: case 228: case 243: case 413: case 423: case 422: case 242: case 183: case 182: case 144: case 241: case 181: case 421: case 1226: case 1242:
             return true;
@@ -125,8 +138,149 @@ constexpr int kSymMaxN = 1 << 26;
 static_assert((kSymMaxN / 32) < (1 << 21) + 1, "worker id must fit the 21-bit tag field");
 
 static bool sym_applies(const hgb_nbody *h) {
-    return h->sym != 0 && h->world == 1 && h->mode == HGB_NBODY_EXACT && h->n >= h->sym_min_n &&
-           h->n < kSymMaxN;
+    if (h->sym == 0 || h->mode != HGB_NBODY_EXACT || h->n < h->sym_min_n || h->n >= kSymMaxN) return false;
+    if (tri_variant(h->sym))   // deals rows over GPUs: single-process handles with peer access
+        return h->world == 1 || (!h->rank_mode && h->exchange == HGB_EXCHANGE_P2P);
+    return h->world == 1;
+}
+
+// ---- second-generation pair-symmetric step (nbody_tri.cuh) ------------------------------------------
+constexpr int kTriDefaultSeg = 8192;
+constexpr long long kTriSpinLimit = 10000000000ll;   // ~5 s of SM clock: a poll that long means a lost hand-off
+
+// tiles (b, k), k <= b, of super-rows b = index (mod world) in anti-diagonal order b + k: both
+// dependencies of a tile, (b, k-1) and (b-1, k), sit on the previous anti-diagonal
+static int tri_plan(hgb_nbody *h, NbShard &s) {
+    const int seg = h->tri_seg > 0 ? h->tri_seg : kTriDefaultSeg;
+    if (s.tri_tiles && s.tri_plan_seg == seg) return HGB_OK;
+    const int T = (h->n + 31) / 32, tr = seg / 32, TS = (T + tr - 1) / tr;
+    std::vector<int2> tiles;
+    for (int d = 0; d <= 2 * (TS - 1); ++d)
+        for (int k = std::max(0, d - TS + 1); 2 * k <= d; ++k) {
+            const int b = d - k;
+            if (b % h->world == s.index) tiles.push_back(make_int2(b, k));
+        }
+    if (s.tri_tiles) cudaFree(s.tri_tiles);
+    s.tri_tiles = nullptr;
+    HGB_CUDA(cudaMalloc(&s.tri_tiles, sizeof(int2) * (tiles.size() + 1)));
+    HGB_CUDA(cudaMemcpyAsync(s.tri_tiles, tiles.data(), sizeof(int2) * tiles.size(), cudaMemcpyHostToDevice, s.dev->stream));
+    HGB_CUDA(cudaStreamSynchronize(s.dev->stream));   // `tiles` goes out of scope
+    s.tri_ntiles = (int)tiles.size();
+    s.tri_plan_seg = seg;
+    return HGB_OK;
+}
+
+static int tri_alloc(hgb_nbody *h) {
+    for (NbShard &s : h->sh) {
+        HGB_CUDA(cudaSetDevice(s.dev->device));
+        if (!s.tri_ctl) {
+            const size_t words = 48ull * h->npad;
+            HGB_CUDA(cudaMalloc(&s.tri_ctl, sizeof(int) * kTriCtlInts));
+            HGB_CUDA(cudaMemsetAsync(s.tri_ctl, 0, sizeof(int) * kTriCtlInts, s.dev->stream));
+            for (int b = 0; b < 2; ++b) {
+                HGB_CUDA(cudaMalloc(&s.tri_ll[b], words));
+                HGB_CUDA(cudaMemsetAsync(s.tri_ll[b], 0, words, s.dev->stream));   // tag 0 is never expected
+            }
+            HGB_CUDA(cudaMalloc(&s.tri_racc, words));
+            HGB_CUDA(cudaMemsetAsync(s.tri_racc, 0, words, s.dev->stream));
+        }
+        HGB_TRY(tri_plan(h, s));
+    }
+    // peers store into these buffers: they must be zeroed before anybody's first step
+    for (NbShard &s : h->sh) HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
+    return HGB_OK;
+}
+
+// shards that share one physical device (HGB_VIRTUAL_GPUS) must fit their persistent grids side by side
+static int tri_shards_on_device(const hgb_nbody *h, const NbShard &s) {
+    int c = 0;
+    for (const NbShard &o : h->sh) c += o.dev->device == s.dev->device;
+    return c;
+}
+
+template <int CTAS, bool PROF>
+static int launch_tri_variant(const TriArgs &a, int grid, cudaStream_t st) {
+    auto kern = nbody_tri_kernel<CTAS, PROF>;
+    static bool attr_done[16] = {false};   // per device: the attribute belongs to the function ON a device
+    int dev = 0;
+    HGB_CUDA(cudaGetDevice(&dev));
+    if (!attr_done[dev & 15]) {
+        HGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTriSmem));
+        attr_done[dev & 15] = true;
+    }
+    kern<<<grid, kTriWarps * 32, kTriSmem, st>>>(a);
+    HGB_LAUNCHED();
+    return HGB_OK;
+}
+
+// one step on every shard: tickets reset, wavefront kernels (all launched before any finish kernel), G*acc of
+// all n bodies from the local copy of the final words, conditional redo by the standard kernel.  Every
+// shard ends with the complete next state: no exchange follows.
+static int launch_tri_step(hgb_nbody *h, int cur, int nxt) {
+    HGB_TRY(tri_alloc(h));
+    const unsigned step = h->tri_step++;
+    const int parity = step & 1;
+    const unsigned epoch_tag = (step % 2047 + 1) << 21;
+    const int seg = h->sh[0].tri_plan_seg, T = (h->n + 31) / 32;
+    const int ctas = h->sym % 10;
+    const bool prof = (h->sym / 10) % 10 == 1;
+    for (NbShard &s : h->sh) {
+        HGB_CUDA(cudaSetDevice(s.dev->device));
+        HGB_CUDA(cudaMemsetAsync(s.tri_ctl, 0, 2 * sizeof(int), s.dev->stream));                       // ticket, range flag
+        HGB_CUDA(cudaMemsetAsync(s.tri_ctl + 8, 0, (kTriCtlInts - 8) * sizeof(int), s.dev->stream));   // profiling counters
+    }
+    if (h->world > 1) {
+        // a peer may raise flags in / publish into this shard's buffers as soon as ITS kernel runs: every
+        // shard's reset must be complete before any wavefront kernel starts
+        for (NbShard &s : h->sh) {
+            HGB_CUDA(cudaSetDevice(s.dev->device));
+            HGB_CUDA(cudaEventRecord(s.dev->ev_step, s.dev->stream));
+        }
+        for (NbShard &s : h->sh)
+            for (NbShard &o : h->sh)
+                if (&o != &s) HGB_CUDA(cudaStreamWaitEvent(s.dev->stream, o.dev->ev_step, 0));
+    }
+    for (NbShard &s : h->sh) {
+        HGB_CUDA(cudaSetDevice(s.dev->device));
+        TriArgs a;
+        memset(&a, 0, sizeof a);
+        a.src = s.state[cur]; a.npad = h->npad; a.n = h->n; a.T = T; a.seg = seg; a.tr = seg / 32;
+        a.tiles = s.tri_tiles; a.ntiles = s.tri_ntiles;
+        a.ll = s.tri_ll[parity];
+        a.ll_down = h->sh[(s.index + 1) % h->world].tri_ll[parity];
+        a.npeers = h->world;
+        for (int p = 0; p < h->world; ++p) { a.ll_all[p] = h->sh[p].tri_ll[parity]; a.ctl_all[p] = h->sh[p].tri_ctl; }
+        a.racc = s.tri_racc; a.epoch_tag = epoch_tag; a.ctl = s.tri_ctl; a.spin_limit = kTriSpinLimit;
+        const int grid = std::max(1, s.dev->sms * ctas / tri_shards_on_device(h, s));
+        int rc = HGB_ERR_ARG;
+        switch (ctas * 2 + (prof ? 1 : 0)) {
+            case 2: rc = launch_tri_variant<1, false>(a, grid, s.dev->stream); break;
+            case 3: rc = launch_tri_variant<1, true>(a, grid, s.dev->stream); break;
+            case 4: rc = launch_tri_variant<2, false>(a, grid, s.dev->stream); break;
+            case 5: rc = launch_tri_variant<2, true>(a, grid, s.dev->stream); break;
+            case 6: rc = launch_tri_variant<3, false>(a, grid, s.dev->stream); break;
+            case 7: rc = launch_tri_variant<3, true>(a, grid, s.dev->stream); break;
+            default: set_error("no nbody_tri variant %d", h->sym);
+        }
+        HGB_TRY(rc);
+    }
+    for (NbShard &s : h->sh) {
+        HGB_CUDA(cudaSetDevice(s.dev->device));
+        // a small persistent grid: while it polls for the final words it must not crowd out a wavefront
+        // kernel that shares the device (virtual shards)
+        const int fgrid = std::min((h->n + 255) / 256, std::max(1, s.dev->sms / tri_shards_on_device(h, s)));
+        nbody_tri_finish_kernel<<<fgrid, 256, 0, s.dev->stream>>>(s.tri_ll[parity], h->npad, h->n,
+                                                                 epoch_tag | (unsigned)T, s.state[nxt], s.tri_ctl,
+                                                                 kTriSpinLimit);
+        HGB_LAUNCHED();
+        // never taken for sane input: an operand left the fast-path range -> the ordinary kernel redoes
+        // the whole step on every shard from the untouched source state
+        PeerOut out;
+        out.count = 1;
+        out.base[0] = s.state[nxt];
+        HGB_TRY(launch_step(h, s, s.state[cur], 0, h->n, nullptr, out, nullptr, s.tri_ctl + 1));
+    }
+    return HGB_OK;
 }
 
 // whole step on shard s: tickets/flags reset, wavefront kernel, G*acc, conditional redo
@@ -181,6 +335,7 @@ static void sym_defaults(hgb_nbody *h) {
         const char *e = getenv("HGB_NBODY_SYM");   // unset: on (default variant); 0: off; else a variant
         int v = e ? atoi(e) : 1;
         if (v == 1) v = kSymDefaultVariant;
+        if (v == 2) v = 2002;
         g_default_sym = sym_variant_known(v) ? v : 0;
     }
     if (g_default_sym_min_n < 0) {
@@ -197,7 +352,8 @@ extern "C" {
 int hgb_nbody_set_symmetric(hgb_nbody *h, int variant, int min_n) {
     HGB_ARG(h, "handle");
     if (variant == 1) variant = kSymDefaultVariant;
-    HGB_ARG(variant == 0 || sym_variant_known(variant), "pair-symmetric variant (R*100 + U*10 + CTAs per SM)");
+    if (variant == 2) variant = 2002;
+    HGB_ARG(variant == 0 || sym_variant_known(variant), "pair-symmetric variant (R*100 + U*10 + CTAs per SM, or 2000 + CTAs per SM)");
     HGB_ARG(min_n >= 0, "min_n");
     h->sym = variant;
     h->sym_min_n = min_n;
@@ -206,11 +362,20 @@ int hgb_nbody_set_symmetric(hgb_nbody *h, int variant, int min_n) {
 
 int hgb_nbody_symmetric(const hgb_nbody *h) { return h && sym_applies(h) ? h->sym : 0; }
 
+int hgb_nbody_set_segment(hgb_nbody *h, int seg) {
+    HGB_ARG(h, "handle");
+    HGB_ARG(seg == 0 || (seg >= 32 && seg % 32 == 0), "segment: a multiple of 32 sources (0 = default)");
+    h->tri_seg = seg;
+    return HGB_OK;
+}
+
 int hgb_nbody_describe(const hgb_nbody *h, char *buf, int capacity) {
     HGB_ARG(h && buf && capacity > 0, "handle / buffer");
     char kern[160];
     const bool fast = h->mode == HGB_NBODY_FAST;
-    if (sym_applies(h)) {
+    if (sym_applies(h) && tri_variant(h->sym)) {
+        snprintf(kern, sizeof kern, "nbody_tri_kernel<%d> seg=%d", h->sym % 10, h->tri_seg > 0 ? h->tri_seg : kTriDefaultSeg);
+    } else if (sym_applies(h)) {
         snprintf(kern, sizeof kern, "nbody_sym_kernel<%d,%d,%d>", h->sym / 100, h->sym / 10 % 10, h->sym % 10);
     } else {
         int block = 0, unroll = 0, warps = 0;
@@ -222,6 +387,7 @@ int hgb_nbody_describe(const hgb_nbody *h, char *buf, int capacity) {
         snprintf(kern, sizeof kern, "nbody_step_kernel<%d,%d,%d,%s>", block, unroll, warps, fast ? "true" : "false");
     }
     const char *xchg = h->world == 1 ? "one GPU, no exchange"
+                     : (sym_applies(h) && tri_variant(h->sym)) ? "pair-symmetric: super-rows of targets dealt round-robin, chain words stored into the next GPU's buffer over NVLink, the last row broadcasts the finished sums (no position exchange)"
                      : h->exchange == HGB_EXCHANGE_P2P ? "targets sharded, results stored into every peer's next state over NVLink (fused epilogue)"
                                                        : "targets sharded, ncclAllGather of positions per step";
     snprintf(buf, (size_t)capacity, "%s | %s", kern, xchg);
@@ -231,16 +397,18 @@ int hgb_nbody_describe(const hgb_nbody *h, char *buf, int capacity) {
 double hgb_nbody_fp64_instr(const hgb_nbody *h) {
     if (!h) return 0.0;
     if (h->mode == HGB_NBODY_FAST) return 16.0;    // FMA-contracted rsqrt-Newton sequence
+    if (sym_applies(h) && tri_variant(h->sym)) return 16.5;   // 264 per 32 x 8 minitile: 26 + 3 per pair + 32 column instructions
     return sym_applies(h) ? 16.0 : 29.0;           // 32 per PAIR (26 + 3 + 3) vs 17 + 8 + 4 per interaction
 }
 
 int hgb_nbody_sym_counters(hgb_nbody *h, unsigned long long *out7) {
     HGB_ARG(h && out7, "handle / out");
     NbShard &s = h->sh[0];
-    if (!s.sym_ctl) { set_error("the pair-symmetric kernel has not run on this handle"); return HGB_ERR_STATE; }
+    int *ctl = tri_variant(h->sym) ? s.tri_ctl : s.sym_ctl;
+    if (!ctl) { set_error("the pair-symmetric kernel has not run on this handle"); return HGB_ERR_STATE; }
     HGB_CUDA(cudaSetDevice(s.dev->device));
     HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
-    HGB_CUDA(cudaMemcpy(out7, s.sym_ctl + 8, 7 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    HGB_CUDA(cudaMemcpy(out7, ctl + 8, 7 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
     return HGB_OK;
 }
 
@@ -270,6 +438,11 @@ int hgb_nbody_destroy(hgb_nbody *h) {
         if (s.tlist) cudaFree(s.tlist);
         if (s.sym_ctl) cudaFree(s.sym_ctl);
         if (s.sym_ll) cudaFree(s.sym_ll);
+        if (s.tri_ctl) cudaFree(s.tri_ctl);
+        if (s.tri_ll[0]) cudaFree(s.tri_ll[0]);
+        if (s.tri_ll[1]) cudaFree(s.tri_ll[1]);
+        if (s.tri_racc) cudaFree(s.tri_racc);
+        if (s.tri_tiles) cudaFree(s.tri_tiles);
     }
     delete h;
     return HGB_OK;
@@ -391,8 +564,14 @@ static int nb_advance(hgb_nbody *h, int iterations, float *ms, bool dyn) {
         HGB_CUDA(cudaSetDevice(s.dev->device));
         HGB_CUDA(cudaEventRecord(s.dev->ev_begin, s.dev->stream));
     }
+    const bool tri = !dyn && sym_applies(h) && tri_variant(h->sym);
     for (int it = 0; it < iterations; ++it) {
         const int cur = h->cur, nxt = cur ^ 1;
+        if (tri) {   // rows dealt over the shards, every shard ends with the whole next state
+            HGB_TRY(launch_tri_step(h, cur, nxt));
+            h->cur = nxt;
+            continue;
+        }
         for (NbShard &s : h->sh) {
             HGB_CUDA(cudaSetDevice(s.dev->device));
             PeerOut out;
@@ -411,7 +590,7 @@ static int nb_advance(hgb_nbody *h, int iterations, float *ms, bool dyn) {
                         s.state[cur], h->npad, h->n, t0, count, nullptr, out, nullptr, d);
                     HGB_LAUNCHED();
                 }
-            } else if (sym_applies(h)) {
+            } else if (sym_applies(h)) {   // first-generation wavefront (variants R*100 + U*10 + CTAs)
                 HGB_TRY(launch_sym(h, s, s.state[cur], out));
             } else {
                 HGB_TRY(launch_step(h, s, s.state[cur], t0, count, nullptr, out, nullptr));
@@ -453,6 +632,18 @@ static int nb_advance(hgb_nbody *h, int iterations, float *ms, bool dyn) {
     }
     HGB_CUDA(cudaGetLastError());
     if (ms) *ms = worst;
+    if (tri && iterations > 0) {   // a hand-off that never arrived: the kernels gave up instead of hanging
+        for (NbShard &s : h->sh) {
+            int flag = 0;
+            HGB_CUDA(cudaSetDevice(s.dev->device));
+            HGB_CUDA(cudaMemcpy(&flag, s.tri_ctl + 2, sizeof(int), cudaMemcpyDeviceToHost));
+            if (flag) {
+                HGB_CUDA(cudaMemset(s.tri_ctl + 2, 0, sizeof(int)));
+                set_error("pair-symmetric wavefront abandoned: a hand-off between rows did not arrive within the spin limit");
+                return HGB_ERR_STATE;
+            }
+        }
+    }
     return HGB_OK;
 }
 

@@ -164,16 +164,28 @@ nbody_tri_kernel(const __grid_constant__ TriArgs a) {
     auto now = [] { return PROF ? clock64() : 0ll; };
 
     // a poll that has lasted too long raises the abort flag everywhere; everyone then runs to the end
-    // without waiting (results are garbage, the host reports the failure)
+    // without waiting (results are garbage, the host reports the failure).  Warp-uniform: every lane calls
+    // it from the same poll loop and all leave together.
     auto give_up = [&](long long t0) -> bool {
-        if (dead) return true;
-        if (*reinterpret_cast<volatile int *>(a.ctl + 2) != 0) { dead = true; return true; }
-        if (clock64() - t0 > a.spin_limit) {
+        bool g = dead;
+        if (!g && *reinterpret_cast<volatile int *>(a.ctl + 2) != 0) g = true;
+        if (!g && clock64() - t0 > a.spin_limit) {
             for (int p = 0; p < a.npeers; ++p) *reinterpret_cast<volatile int *>(a.ctl_all[p] + 2) = 1;
-            dead = true;
-            return true;
+            g = true;
         }
-        return false;
+        dead = __any_sync(FULL, g);
+        return dead;
+    };
+    // an operand left the range of the branch-free IEEE sequences (never for sane finite positions): the
+    // flag is raised on every GPU BEFORE anything computed from it is published, so whoever sees the
+    // final words of the step also sees the flag, and the ordinary kernel redoes the step everywhere
+    bool raised = false;
+    auto check_range = [&]() {
+        if (!raised && __any_sync(FULL, key >= kRangeLimit)) {
+            for (int p = 0; p < a.npeers; ++p) *reinterpret_cast<volatile int *>(a.ctl_all[p] + 1) = 1;
+            __threadfence_system();
+            raised = true;
+        }
     };
 
     for (;;) {
@@ -214,6 +226,7 @@ nbody_tri_kernel(const __grid_constant__ TriArgs a) {
         // chain word of (minitile mt of chunk ch) for this column lane
         auto word_index = [&](int chunk, int mt) { return (size_t)chunk * 96 + cc * 32 + mt * 8 + cu; };
         auto publish = [&](int chunk, int mt, double chain) {
+            check_range();
             if (lane >= 24) return;
             const ulonglong2 w = ll_pack(chain, my_tag);
             const size_t at = word_index(chunk, mt);
@@ -344,8 +357,7 @@ nbody_tri_kernel(const __grid_constant__ TriArgs a) {
         atomicAdd(c + 2, (unsigned long long)t_item); atomicAdd(c + 3, (unsigned long long)t_diag);
         atomicAdd(c + 4, (unsigned long long)n_items);
     }
-    if (key >= kRangeLimit)
-        for (int p = 0; p < a.npeers; ++p) *reinterpret_cast<volatile int *>(a.ctl_all[p] + 1) = 1;
+    check_range();
 }
 
 // buffer[i] = G * acc[i] (reference src/nbody/nbody-run.c:22-24).  acc = what the LAST row published (tag
@@ -354,20 +366,21 @@ nbody_tri_kernel(const __grid_constant__ TriArgs a) {
 __global__ void __launch_bounds__(256)
 nbody_tri_finish_kernel(const ulonglong2 *__restrict__ ll, int npad, int n, unsigned final_tag, double *out,
                         int *ctl, long long spin_limit) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const ulonglong2 *q = ll + (size_t)(i >> 5) * 96 + (i & 31);
-    ulonglong2 wx = ll_load(q), wy = ll_load(q + 32), wz = ll_load(q + 64);
-    const long long t0 = clock64();
-    while (!(ll_ok(wx, final_tag) && ll_ok(wy, final_tag) && ll_ok(wz, final_tag))) {
-        if (*reinterpret_cast<volatile int *>(ctl + 2) != 0) break;
-        if (clock64() - t0 > spin_limit) { *reinterpret_cast<volatile int *>(ctl + 2) = 1; break; }
-        __nanosleep(200);
-        wx = ll_load(q); wy = ll_load(q + 32); wz = ll_load(q + 64);
+    // a small persistent grid (grid-stride): while it polls it must not crowd out a wavefront kernel
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const ulonglong2 *q = ll + (size_t)(i >> 5) * 96 + (i & 31);
+        ulonglong2 wx = ll_load(q), wy = ll_load(q + 32), wz = ll_load(q + 64);
+        const long long t0 = clock64();
+        while (!(ll_ok(wx, final_tag) && ll_ok(wy, final_tag) && ll_ok(wz, final_tag))) {
+            if (*reinterpret_cast<volatile int *>(ctl + 2) != 0) break;
+            if (clock64() - t0 > spin_limit) { *reinterpret_cast<volatile int *>(ctl + 2) = 1; break; }
+            __nanosleep(200);
+            wx = ll_load(q); wy = ll_load(q + 32); wz = ll_load(q + 64);
+        }
+        out[i] = __dmul_rn(kG, ll_unpack(wx));
+        out[(size_t)npad + i] = __dmul_rn(kG, ll_unpack(wy));
+        out[2 * (size_t)npad + i] = __dmul_rn(kG, ll_unpack(wz));
     }
-    out[i] = __dmul_rn(kG, ll_unpack(wx));
-    out[(size_t)npad + i] = __dmul_rn(kG, ll_unpack(wy));
-    out[2 * (size_t)npad + i] = __dmul_rn(kG, ll_unpack(wz));
 }
 
 }  // namespace hgb

@@ -70,6 +70,11 @@ class NBody:
         check(lib().hgb_nbody_set_symmetric(self._h, int(variant), int(min_n)))
         return self
 
+    def segment(self, seg=0):
+        """sources per segment of the second-generation pair-symmetric kernel (multiple of 32; 0 = default)"""
+        check(lib().hgb_nbody_set_segment(self._h, int(seg)))
+        return self
+
     def describe(self):
         """(kernel, parallelism) the next step() will use on this handle as configured now"""
         buf = C.create_string_buffer(512)

@@ -97,6 +97,13 @@ int hgb_nbody_tune(hgb_nbody *h, int block, int unroll, int warps);
  * the GPU).  New handles default to variant 1 with min_n = 393216 (env HGB_NBODY_SYM = 0 | 1 | variant
  * and HGB_NBODY_SYM_MIN_N override); hgb_nbody_tune with a non-zero argument switches it off. */
 int hgb_nbody_set_symmetric(hgb_nbody *h, int variant, int min_n);
+/* Variants 2000 + C (C = 1..3 CTAs per SM; 2 = 2002; 2010 + C: with clock64 span counters) select the
+ * second-generation pair-symmetric kernel (csrc/nbody_tri.cuh): forces evaluated per 32 x 8 minitile, the
+ * ordered accumulation decoupled from them (row pass in registers, column pass through a shared-memory
+ * transpose), rows cut into segments of `seg` sources (hgb_nbody_set_segment; 0 = 8192).  It also runs on
+ * single-process multi-GPU handles with HGB_EXCHANGE_P2P: super-rows of targets are dealt over the GPUs,
+ * the chain words cross NVLink as tagged stores, the last row broadcasts the finished sums. */
+int hgb_nbody_set_segment(hgb_nbody *h, int seg);
 /* the variant hgb_nbody_step will use on this handle as configured now (0: the standard kernel) */
 int hgb_nbody_symmetric(const hgb_nbody *h);
 /* "<kernel> | <how targets/pairs are spread over the GPUs>" of the next hgb_nbody_step on this handle
