@@ -11,8 +11,8 @@
 No CPU fallback: compute entry points raise when libhgb200.so or a GPU is missing.
 """
 from . import _abi, convolution, dist, nbody, synth  # noqa: F401
-from ._abi import (EXCHANGE_NCCL, EXCHANGE_P2P, NBODY_EXACT, NBODY_FAST, HgbError,  # noqa: F401
-                   lib)
+from ._abi import (CONV_EXACT, CONV_FAST, EXCHANGE_NCCL, EXCHANGE_P2P, NBODY_EXACT,  # noqa: F401
+                   NBODY_FAST, HgbError, lib)
 
 __all__ = ["nbody", "convolution", "dist", "synth", "lib", "HgbError", "NBODY_EXACT",
-           "NBODY_FAST", "EXCHANGE_NCCL", "EXCHANGE_P2P"]
+           "NBODY_FAST", "EXCHANGE_NCCL", "EXCHANGE_P2P", "CONV_EXACT", "CONV_FAST"]

@@ -12,6 +12,7 @@ LIB_PATH = os.path.join(_HERE, "libhgb200.so")
 HGB_OK = 0
 HGB_ERR_ARG, HGB_ERR_CUDA, HGB_ERR_NCCL, HGB_ERR_STATE, HGB_ERR_NOGPU = -1, -2, -3, -4, -5
 NBODY_EXACT, NBODY_FAST = 0, 1
+CONV_EXACT, CONV_FAST = 0, 1
 EXCHANGE_NCCL, EXCHANGE_P2P = 0, 1
 UNIQUE_ID_BYTES = 128
 
@@ -46,7 +47,7 @@ SIGNATURES = {
     "hgb_nbody_tune": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int]),
     "hgb_nbody_set_symmetric": (C.c_int, [_vp, C.c_int, C.c_int]),
     "hgb_nbody_symmetric": (C.c_int, [_vp]),
-    "hgb_nbody_set_segment": (C.c_int, [_vp, C.c_int]),
+    "hgb_nbody_set_segment": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int]),
     "hgb_nbody_describe": (C.c_int, [_vp, C.c_char_p, C.c_int]),
     "hgb_nbody_fp64_instr": (C.c_double, [_vp]),
     "hgb_nbody_sym_counters": (C.c_int, [_vp, C.POINTER(C.c_ulonglong)]),
@@ -64,6 +65,9 @@ SIGNATURES = {
     "hgb_selftest_inv_sqrt": (C.c_int, [C.c_ulonglong, C.c_ulonglong, C.POINTER(C.c_ulonglong), _dp]),
     "hgb_conv_run": (C.c_int, [_dp, _dp, C.c_int, C.c_int, C.c_int, _dp, C.c_int, C.c_int, C.c_int,
                                C.c_int]),
+    "hgb_set_conv_mode": (C.c_int, [C.c_int]),
+    "hgb_conv_set_mode": (C.c_int, [_vp, C.c_int]),
+    "hgb_conv_mode_in_effect": (C.c_int, [_vp]),
     "hgb_conv_create": (C.c_int, [C.POINTER(_vp), C.c_int, C.c_int, C.c_int, C.c_int]),
     "hgb_conv_create_rank": (C.c_int, [C.POINTER(_vp), C.c_int, C.c_int, C.c_int]),
     "hgb_conv_set_kernel": (C.c_int, [_vp, _dp, C.c_int, C.c_int]),

@@ -210,6 +210,15 @@ class Conv2D:
         check(lib().hgb_conv_set_kernel(self._h, dptr(kernel), kw, kh))
         return self
 
+    def set_mode(self, mode):
+        """CONV_EXACT (bit-identical, default) or CONV_FAST (fused multiply-add taps; floating-point images
+        only -- an integer-valued image keeps the exact kernels); choose it before upload()"""
+        check(lib().hgb_conv_set_mode(self._h, int(mode)))
+        return self
+
+    def mode_in_effect(self):
+        return lib().hgb_conv_mode_in_effect(self._h)
+
     def tune(self, variant=0, band_rows=0):
         check(lib().hgb_conv_tune(self._h, int(variant), int(band_rows)))
         return self

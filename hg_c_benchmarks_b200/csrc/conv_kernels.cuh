@@ -38,11 +38,21 @@ struct BandGeom {
     int dp;          // device row pitch in doubles
 };
 
+// One tap.  EXACT: val + k*v as the reference computes it under ISO C (no contraction): one rounding for
+// the product, one for the sum (reference src/convolution/convolution-run.c:71-77).  FAST (opt-in, floating-
+// point images only, never the parity path): one fused multiply-add -- half the FP64 instructions, a
+// single rounding per tap, results within ~1e-15 relative per iteration of the exact ones.
+template <bool FAST>
+__device__ __forceinline__ double conv_tap(double val, double k, double v) {
+    return FAST ? __fma_rn(k, v, val) : __dadd_rn(val, __dmul_rn(k, v));
+}
+
 __device__ __forceinline__ size_t band_row_off(const BandGeom &g, int gr) {
     return (size_t)(gr - g.row0 + g.halo) * g.dp;
 }
 
 // ---- generic fallback: any kw, kh <= 2p+1 --------------------------------
+template <bool FAST = false>
 __global__ void __launch_bounds__(256)
 conv_generic_kernel(const double *__restrict__ in, double *__restrict__ out, BandGeom g,
                     const double *__restrict__ taps, int kw, int kh) {
@@ -53,7 +63,7 @@ conv_generic_kernel(const double *__restrict__ in, double *__restrict__ out, Ban
     for (int ky = 0; ky < kh; ++ky) {
         const int gr = min(max(y + ky - g.p, 0), g.H - 1);
         const double *row = in + band_row_off(g, gr) + kLead - g.p + x;   // padded column x + kx
-        for (int kx = 0; kx < kw; ++kx) val = __dadd_rn(val, __dmul_rn(taps[ky * kw + kx], row[kx]));
+        for (int kx = 0; kx < kw; ++kx) val = conv_tap<FAST>(val, taps[ky * kw + kx], row[kx]);
     }
     double *orow = out + band_row_off(g, y) + kLead;
     orow[x] = val;
@@ -82,7 +92,7 @@ struct ConvCfg {
     static constexpr size_t SMEM = (size_t)NST * STAGE_ROWS * ROWW * sizeof(double) + NST * 8;
 };
 
-template <int K, int TW, int C, int NST>
+template <int K, int TW, int C, int NST, bool FAST = false>
 __global__ void __launch_bounds__(TW / C)
 conv_stream_kernel(const double *__restrict__ in, double *__restrict__ out, BandGeom g, int chunk,
                    const __grid_constant__ Taps taps) {
@@ -158,7 +168,7 @@ conv_stream_kernel(const double *__restrict__ in, double *__restrict__ out, Band
                             double val = (ky == 0) ? 0.0 : acc[a][c];
 #pragma unroll
                             for (int kx = 0; kx < K; ++kx)
-                                val = __dadd_rn(val, __dmul_rn(taps.k[ky * K + kx], v[c + kx]));
+                                val = conv_tap<FAST>(val, taps.k[ky * K + kx], v[c + kx]);
                             acc[a][c] = val;
                         }
                         if (ky == K - 1 && any_col && (EDGE || i >= K - 1)) {   // output row i-(K-1) is complete
@@ -219,7 +229,7 @@ constexpr size_t kF2Smem = (size_t)(kF2Ring + 2) * kF2Pitch * sizeof(double) + k
 // C = columns per thread (2 or 4); kF2TW / C threads per CTA.  Measured equal on B200 (a pass moves
 // 4.39 GB, so its HBM floor is ~650 us; both variants take ~800 us for two iterations with the FP64
 // pipe ~69 % busy, ncu: profiles/r1c_conv3_fused_ncu_summary.txt); C = 2 is the default.
-template <int C>
+template <int C, bool FAST = false>
 __global__ void __launch_bounds__(kF2TW / C)
 conv3_fused2_kernel(const double *__restrict__ in, double *__restrict__ out, BandGeom g, int chunk,
                     const __grid_constant__ Taps taps) {
@@ -315,7 +325,7 @@ conv3_fused2_kernel(const double *__restrict__ in, double *__restrict__ out, Ban
                     for (int c = 0; c < C; ++c) {
                         double val = (ky == 0) ? 0.0 : a1[sl][c];
 #pragma unroll
-                        for (int kx = 0; kx < 3; ++kx) val = __dadd_rn(val, __dmul_rn(taps.k[ky * 3 + kx], v[c + kx]));
+                        for (int kx = 0; kx < 3; ++kx) val = conv_tap<FAST>(val, taps.k[ky * 3 + kx], v[c + kx]);
                         a1[sl][c] = val;
                     }
                 }
@@ -358,13 +368,13 @@ conv3_fused2_kernel(const double *__restrict__ in, double *__restrict__ out, Ban
                         if (EDGE && top) { // intermediate row -1 aliases row 0: tap row 0 comes from this row too
                             val = 0.0;
 #pragma unroll
-                            for (int kx = 0; kx < 3; ++kx) val = __dadd_rn(val, __dmul_rn(taps.k[kx], w[c + kx]));
+                            for (int kx = 0; kx < 3; ++kx) val = conv_tap<FAST>(val, taps.k[kx], w[c + kx]);
                         }
 #pragma unroll
-                        for (int kx = 0; kx < 3; ++kx) val = __dadd_rn(val, __dmul_rn(taps.k[ky * 3 + kx], w[c + kx]));
+                        for (int kx = 0; kx < 3; ++kx) val = conv_tap<FAST>(val, taps.k[ky * 3 + kx], w[c + kx]);
                         if (EDGE && bottom) {   // intermediate row H aliases row H-1: tap row 2 from this row as well
 #pragma unroll
-                            for (int kx = 0; kx < 3; ++kx) val = __dadd_rn(val, __dmul_rn(taps.k[6 + kx], w[c + kx]));
+                            for (int kx = 0; kx < 3; ++kx) val = conv_tap<FAST>(val, taps.k[6 + kx], w[c + kx]);
                         }
                         a2[sl][c] = val;
                     }
@@ -543,6 +553,21 @@ conv_pad_columns_kernel(double *__restrict__ img, BandGeom g, int r0, int r1) {
     double *row = img + band_row_off(g, y) + kLead;
     const double left = row[0], right = row[g.W - 1];
     for (int q = i; q < g.p; q += 8) { row[-1 - q] = left; row[g.W + q] = right; }
+}
+
+// FAST mode guard: is every inner pixel of rows [r0, r1) an integer-valued double?  (north_star: integer
+// images must stay bit-exact, so they keep the exact kernels even when FAST is requested.)  flag[0] is
+// set to 1 by any thread that finds a non-integer (or non-finite) pixel.
+__global__ void __launch_bounds__(256)
+conv_not_integer_kernel(const double *__restrict__ img, BandGeom g, int r0, int r1, int *flag) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= g.W) return;
+    bool bad = false;
+    for (int y = r0 + blockIdx.y; y < r1; y += gridDim.y) {
+        const double v = img[band_row_off(g, y) + kLead + x];
+        bad |= !(v == rint(v)) || !(fabs(v) <= 9007199254740992.0);
+    }
+    if (bad) flag[0] = 1;
 }
 
 // sequential row-major checksum (reference get_checksum, convolution-util.c:63-71):

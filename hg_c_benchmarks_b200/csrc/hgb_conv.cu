@@ -39,6 +39,9 @@ struct hgb_conv {
     bool uploaded = false;
     bool have_backup = false;
     int bak_valid_xr = 0;
+    int mode = HGB_CONV_EXACT;    // HGB_CONV_FAST: fused multiply-add taps, floating-point images only
+    bool integer_input = false;   // the uploaded image was integer-valued: exact kernels even in FAST mode
+    bool bak_integer_input = false;
     std::vector<CvShard> sh;
 };
 
@@ -50,6 +53,9 @@ static BandGeom geom(const hgb_conv *h, const CvShard &s) {
     g.halo = h->halo; g.dp = h->dp;
     return g;
 }
+
+// FAST arithmetic applies to floating-point images only (north_star: integer images stay bit-exact)
+static bool use_fast(const hgb_conv *h) { return h->mode == HGB_CONV_FAST && !h->integer_input; }
 
 // band i of `active` equal bands (first H % active bands get one extra row)
 static void band_of(int H, int active, int i, int *row0, int *rows) {
@@ -104,11 +110,12 @@ template <int K, int NST>
 static int launch_stream(const hgb_conv *h, const CvShard &s, const double *in, double *out, int crow0,
                          int crows, cudaStream_t st) {
     using Cfg = ConvCfg<K, kTW, 2, NST>;
-    auto kern = conv_stream_kernel<K, kTW, 2, NST>;
-    static bool attr_done[16] = {false};
-    if (!attr_done[s.dev->device & 15]) {
+    const bool fast = use_fast(h);
+    auto kern = fast ? conv_stream_kernel<K, kTW, 2, NST, true> : conv_stream_kernel<K, kTW, 2, NST, false>;
+    static bool attr_done[2][16] = {{false}};
+    if (!attr_done[fast][s.dev->device & 15]) {
         HGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
-        attr_done[s.dev->device & 15] = true;
+        attr_done[fast][s.dev->device & 15] = true;
     }
     // output rows per CTA: small chunks keep the concurrently streamed rows close together in
     // DRAM (3x3 is HBM-bound); larger ones amortise the K-1 extra input rows (5x5, 7x7 are
@@ -133,14 +140,17 @@ static int launch_fused2(const hgb_conv *h, const CvShard &s, const double *in, 
     BandGeom g = geom(h, s);
     g.crow0 = crow0;
     g.crows = crows;
-    if (h->fuse_warp) {
+    if (h->fuse_warp && !use_fast(h)) {
         dim3 gridw((h->W + kF2wOut - 1) / kF2wOut, (crows + chunk - 1) / chunk);
         conv3_fused2w_kernel<<<gridw, kF2wWarps * 32, kF2wSmem, st>>>(in, out, g, chunk, h->taps);
         HGB_LAUNCHED();
         return HGB_OK;
     }
     dim3 grid((h->W + kF2Out - 1) / kF2Out, (crows + chunk - 1) / chunk);
-    if (h->fuse_cols == 2) conv3_fused2_kernel<2><<<grid, kF2TW / 2, kF2Smem, st>>>(in, out, g, chunk, h->taps);
+    if (use_fast(h)) {
+        if (h->fuse_cols == 2) conv3_fused2_kernel<2, true><<<grid, kF2TW / 2, kF2Smem, st>>>(in, out, g, chunk, h->taps);
+        else conv3_fused2_kernel<4, true><<<grid, kF2TW / 4, kF2Smem, st>>>(in, out, g, chunk, h->taps);
+    } else if (h->fuse_cols == 2) conv3_fused2_kernel<2><<<grid, kF2TW / 2, kF2Smem, st>>>(in, out, g, chunk, h->taps);
     else conv3_fused2_kernel<4><<<grid, kF2TW / 4, kF2Smem, st>>>(in, out, g, chunk, h->taps);
     HGB_LAUNCHED();
     return HGB_OK;
@@ -159,7 +169,8 @@ static int launch_conv(const hgb_conv *h, const CvShard &s, const double *in, do
     g.crow0 = crow0;
     g.crows = crows;
     dim3 grid((h->W + 255) / 256, crows);
-    conv_generic_kernel<<<grid, 256, 0, st>>>(in, out, g, s.taps_dev, h->kw, h->kh);
+    if (use_fast(h)) conv_generic_kernel<true><<<grid, 256, 0, st>>>(in, out, g, s.taps_dev, h->kw, h->kh);
+    else conv_generic_kernel<false><<<grid, 256, 0, st>>>(in, out, g, s.taps_dev, h->kw, h->kh);
     HGB_LAUNCHED();
     return HGB_OK;
 }
@@ -249,6 +260,8 @@ int hgb_conv_destroy(hgb_conv *h) {
     delete h;
     return HGB_OK;
 }
+
+static int cv_classify(hgb_conv *h);   // FAST mode: integer-valued images keep the exact kernels
 
 static int cv_check_dims(int w, int hh, int p) {
     HGB_ARG(w > 0 && hh > 0, "image size must be positive");
@@ -372,9 +385,55 @@ int hgb_conv_upload(hgb_conv *h, const double *cur) {
     h->uploaded = true;
     h->valid_xr = h->rank_mode ? 0 : h->halo;
     if (h->rank_mode && h->world > 1) HGB_TRY(halo_exchange(h, 0));
+    HGB_TRY(cv_classify(h));
     for (CvShard &s : h->sh) HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
     return HGB_OK;
 }
+
+// FAST mode: classify the image just uploaded into state 0 (integer-valued images keep the exact kernels).
+// One pass over the band; skipped entirely in EXACT mode.
+static int cv_classify(hgb_conv *h) {
+    h->integer_input = false;
+    if (h->mode != HGB_CONV_FAST) return HGB_OK;
+    bool all_int = true;
+    for (CvShard &s : h->sh) {
+        if (s.rows <= 0) continue;
+        HGB_CUDA(cudaSetDevice(s.dev->device));
+        int *flag = reinterpret_cast<int *>(s.scratch) + 8;
+        HGB_CUDA(cudaMemsetAsync(flag, 0, sizeof(int), s.dev->stream));
+        dim3 grid((h->W + 255) / 256, std::min(s.rows, 64));
+        conv_not_integer_kernel<<<grid, 256, 0, s.dev->stream>>>(s.img[0], geom(h, s), s.row0, s.row0 + s.rows, flag);
+        HGB_LAUNCHED();
+        int host_flag = 0;
+        HGB_CUDA(cudaMemcpyAsync(&host_flag, flag, sizeof(int), cudaMemcpyDeviceToHost, s.dev->stream));
+        HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
+        all_int = all_int && host_flag == 0;
+    }
+    if (h->rank_mode && h->world > 1) {
+        // every rank must take the same kernels: the image is integer-valued only if every band is
+        double v = all_int ? 0.0 : 1.0, *d = reinterpret_cast<double *>(h->sh[0].scratch);
+        cudaStream_t st = h->sh[0].dev->stream;
+        HGB_CUDA(cudaMemcpyAsync(d, &v, sizeof v, cudaMemcpyHostToDevice, st));
+        HGB_NCCL(nccl().AllReduce(d, d, 1, ncclDouble, ncclSum, rt().rank_comm, st));
+        HGB_CUDA(cudaMemcpyAsync(&v, d, sizeof v, cudaMemcpyDeviceToHost, st));
+        HGB_CUDA(cudaStreamSynchronize(st));
+        all_int = v == 0.0;
+    }
+    h->integer_input = all_int;
+    return HGB_OK;
+}
+
+int hgb_conv_set_mode(hgb_conv *h, int mode) {
+    HGB_ARG(h && (mode == HGB_CONV_EXACT || mode == HGB_CONV_FAST), "handle / mode");
+    if (mode == HGB_CONV_FAST && h->mode != HGB_CONV_FAST && h->uploaded) {
+        set_error("hgb_conv_set_mode(FAST) must precede the upload (the image is classified there)");
+        return HGB_ERR_STATE;
+    }
+    h->mode = mode;
+    return HGB_OK;
+}
+
+int hgb_conv_mode_in_effect(const hgb_conv *h) { return h && use_fast(h) ? HGB_CONV_FAST : HGB_CONV_EXACT; }
 
 int hgb_conv_step(hgb_conv *h, int iterations, float *ms) {
     HGB_ARG(h && iterations >= 0, "handle / iterations");
@@ -545,6 +604,7 @@ int hgb_conv_upload_dense(hgb_conv *h, const double *dense) {
     h->uploaded = true;
     h->valid_xr = h->rank_mode ? 0 : h->halo;
     if (h->rank_mode && h->world > 1) HGB_TRY(halo_exchange(h, 0));
+    HGB_TRY(cv_classify(h));
     for (CvShard &s : h->sh) HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
     return HGB_OK;
 }
@@ -581,6 +641,7 @@ int hgb_conv_backup(hgb_conv *h) {
     for (CvShard &s : h->sh) HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
     h->have_backup = true;
     h->bak_valid_xr = h->valid_xr;
+    h->bak_integer_input = h->integer_input;
     return HGB_OK;
 }
 
@@ -594,6 +655,7 @@ int hgb_conv_restore(hgb_conv *h) {
     }
     for (CvShard &s : h->sh) HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
     h->valid_xr = h->bak_valid_xr;
+    h->integer_input = h->bak_integer_input;
     return HGB_OK;
 }
 
@@ -621,6 +683,13 @@ int hgb_conv_checksum(hgb_conv *h, double *checksum) {
 static hgb_conv *g_cv = nullptr;
 static int g_cv_key[4] = {0, 0, 0, 0};
 static int g_cv_exchange = HGB_EXCHANGE_NCCL;
+static int g_cv_mode = -1;   // -1: read HGB_CONV_FAST from the environment on first use
+
+int hgb_set_conv_mode(int mode) {
+    HGB_ARG(mode == HGB_CONV_EXACT || mode == HGB_CONV_FAST, "mode");
+    g_cv_mode = mode;
+    return HGB_OK;
+}
 
 int hgb_conv_run(double *cur, double *prev, int inner_w, int inner_h, int padding,
                  const double *kernel, int kw, int kh, int iterations, int ngpus) {
@@ -639,6 +708,12 @@ int hgb_conv_run(double *cur, double *prev, int inner_w, int inner_h, int paddin
         HGB_TRY(hgb_conv_create(&g_cv, inner_w, inner_h, padding, g));
         g_cv_key[0] = inner_w; g_cv_key[1] = inner_h; g_cv_key[2] = padding; g_cv_key[3] = g;
     }
+    if (g_cv_mode < 0) {
+        const char *e = getenv("HGB_CONV_FAST");
+        g_cv_mode = (e && atoi(e) != 0) ? HGB_CONV_FAST : HGB_CONV_EXACT;
+    }
+    g_cv->uploaded = false;   // a new image follows: the mode may change
+    HGB_TRY(hgb_conv_set_mode(g_cv, g_cv_mode));
     HGB_TRY(hgb_conv_set_exchange(g_cv, g_cv_exchange));
     HGB_TRY(hgb_conv_set_kernel(g_cv, kernel, kw, kh));
     HGB_TRY(hgb_conv_upload(g_cv, cur));

@@ -1,6 +1,8 @@
 // hgb_nbody.cu -- host side of the nbody path: device-resident handle, target
 // sharding, position exchange (ncclAllGather or fused peer stores) and the
 // drop-in for the reference's run() (src/nbody/nbody-run.c:27-37).
+#include <algorithm>
+
 #include "hgb_common.cuh"
 #include "nbody_kernels.cuh"
 #include "nbody_sym.cuh"
@@ -29,7 +31,7 @@ struct NbShard {
     ulonglong2 *tri_ll[2] = {nullptr, nullptr};   // chain words, double-buffered by step parity, 48 B per body each
     ulonglong2 *tri_racc = nullptr;               // row accumulators between the items of a row, 48 B per body
     int2 *tri_tiles = nullptr;                    // this shard's tiles in ticket order
-    int tri_ntiles = 0, tri_plan_seg = 0;
+    int tri_ntiles = 0, tri_plan_seg = 0, tri_plan_rows = 0, tri_plan_weight = 0;
 };
 }  // namespace
 
@@ -43,7 +45,9 @@ struct hgb_nbody {
     bool dynamics = false;  // hgb_nbody_set_dynamics was called
     int sym = 0;            // pair-symmetric kernel variant R*100 + U*10 + CTAs/SM (0 = off)
     int sym_min_n = 0;      // ... used when n >= sym_min_n, one GPU, EXACT mode
-    int tri_seg = 0;        // second-generation kernel (variants 2000+): sources per segment
+    int tri_seg = 0;        // second-generation kernel (variants 2000+): sources per segment,
+    int tri_rows = 0;       // ... rows per tile,
+    int tri_weight = 0;     // ... weight of the segment index in the ticket order (0 = defaults)
     unsigned tri_step = 0;  // steps run with it so far (epoch and buffer parity)
     int tri_status = 0;     // abort flag read back after the last advance
     double dt = 0.0;
@@ -145,28 +149,39 @@ static bool sym_applies(const hgb_nbody *h) {
 }
 
 // ---- second-generation pair-symmetric step (nbody_tri.cuh) ------------------------------------------
-constexpr int kTriDefaultSeg = 8192;
+constexpr int kTriDefaultSeg = 8192;      // sources per item
+constexpr int kTriDefaultRows = 16;       // rows per tile: rows of a tile start together and then stagger themselves
+constexpr int kTriDefaultWeight = 16;     // ticket order key = tile-row + weight * segment
 constexpr long long kTriSpinLimit = 10000000000ll;   // ~5 s of SM clock: a poll that long means a lost hand-off
 
-// tiles (b, k), k <= b, of super-rows b = index (mod world) in anti-diagonal order b + k: both
-// dependencies of a tile, (b, k-1) and (b-1, k), sit on the previous anti-diagonal
+// Tiles (b, k): the `tr` rows of tile-row b against segment k, for every segment some row of b reaches.
+// Item (I, k) needs (I, k-1) finished and streams the words of (I-1, k), or -- where row I-1 ends before
+// segment k -- of row I-1's last item (I-1, k-1).  Ticket order: key b + weight * k ascending (then k): all
+// three predecessors have a smaller key, so the order is a linear extension of the dependencies for any
+// weight >= 1; the weight spaces the segments of one row far enough apart in the ticket stream that item
+// (I, k-1) is finished when (I, k) is handed out.  Tile-row b lives on shard b mod world.
 static int tri_plan(hgb_nbody *h, NbShard &s) {
     const int seg = h->tri_seg > 0 ? h->tri_seg : kTriDefaultSeg;
-    if (s.tri_tiles && s.tri_plan_seg == seg) return HGB_OK;
-    const int T = (h->n + 31) / 32, tr = seg / 32, TS = (T + tr - 1) / tr;
-    std::vector<int2> tiles;
-    for (int d = 0; d <= 2 * (TS - 1); ++d)
-        for (int k = std::max(0, d - TS + 1); 2 * k <= d; ++k) {
-            const int b = d - k;
-            if (b % h->world == s.index) tiles.push_back(make_int2(b, k));
-        }
+    const int tr = h->tri_rows > 0 ? h->tri_rows : kTriDefaultRows;
+    const int weight = h->tri_weight > 0 ? h->tri_weight : kTriDefaultWeight;
+    if (s.tri_tiles && s.tri_plan_seg == seg && s.tri_plan_rows == tr && s.tri_plan_weight == weight) return HGB_OK;
+    const int T = (h->n + 31) / 32, TB = (T + tr - 1) / tr;
+    std::vector<std::pair<long long, int2>> keyed;
+    for (int b = s.index; b < TB; b += h->world) {
+        const long long last_row = std::min(T - 1, b * tr + tr - 1);
+        const int kmax = (int)(32 * last_row / seg);
+        for (int k = 0; k <= kmax; ++k) keyed.push_back({((long long)b + (long long)weight * k) * 4096 + k, make_int2(b, k)});
+    }
+    std::sort(keyed.begin(), keyed.end(), [](const auto &x, const auto &y) { return x.first < y.first; });
+    std::vector<int2> tiles(keyed.size());
+    for (size_t i = 0; i < keyed.size(); ++i) tiles[i] = keyed[i].second;
     if (s.tri_tiles) cudaFree(s.tri_tiles);
     s.tri_tiles = nullptr;
     HGB_CUDA(cudaMalloc(&s.tri_tiles, sizeof(int2) * (tiles.size() + 1)));
     HGB_CUDA(cudaMemcpyAsync(s.tri_tiles, tiles.data(), sizeof(int2) * tiles.size(), cudaMemcpyHostToDevice, s.dev->stream));
     HGB_CUDA(cudaStreamSynchronize(s.dev->stream));   // `tiles` goes out of scope
     s.tri_ntiles = (int)tiles.size();
-    s.tri_plan_seg = seg;
+    s.tri_plan_seg = seg; s.tri_plan_rows = tr; s.tri_plan_weight = weight;
     return HGB_OK;
 }
 
@@ -221,7 +236,7 @@ static int launch_tri_step(hgb_nbody *h, int cur, int nxt) {
     const unsigned step = h->tri_step++;
     const int parity = step & 1;
     const unsigned epoch_tag = (step % 2047 + 1) << 21;
-    const int seg = h->sh[0].tri_plan_seg, T = (h->n + 31) / 32;
+    const int seg = h->sh[0].tri_plan_seg, rows = h->sh[0].tri_plan_rows, T = (h->n + 31) / 32;
     const int ctas = h->sym % 10;
     const bool prof = (h->sym / 10) % 10 == 1;
     for (NbShard &s : h->sh) {
@@ -244,10 +259,10 @@ static int launch_tri_step(hgb_nbody *h, int cur, int nxt) {
         HGB_CUDA(cudaSetDevice(s.dev->device));
         TriArgs a;
         memset(&a, 0, sizeof a);
-        a.src = s.state[cur]; a.npad = h->npad; a.n = h->n; a.T = T; a.seg = seg; a.tr = seg / 32;
+        a.src = s.state[cur]; a.npad = h->npad; a.n = h->n; a.T = T; a.seg = seg; a.tr = rows;
         a.tiles = s.tri_tiles; a.ntiles = s.tri_ntiles;
         a.ll = s.tri_ll[parity];
-        a.ll_down = h->sh[(s.index + 1) % h->world].tri_ll[parity];
+        a.ll_down = h->sh[(s.index + 1) % h->world].tri_ll[parity];   // tile-row b+1 lives on the next shard
         a.npeers = h->world;
         for (int p = 0; p < h->world; ++p) { a.ll_all[p] = h->sh[p].tri_ll[parity]; a.ctl_all[p] = h->sh[p].tri_ctl; }
         a.racc = s.tri_racc; a.epoch_tag = epoch_tag; a.ctl = s.tri_ctl; a.spin_limit = kTriSpinLimit;
@@ -362,10 +377,13 @@ int hgb_nbody_set_symmetric(hgb_nbody *h, int variant, int min_n) {
 
 int hgb_nbody_symmetric(const hgb_nbody *h) { return h && sym_applies(h) ? h->sym : 0; }
 
-int hgb_nbody_set_segment(hgb_nbody *h, int seg) {
+int hgb_nbody_set_segment(hgb_nbody *h, int seg, int rows_per_tile, int order_weight) {
     HGB_ARG(h, "handle");
     HGB_ARG(seg == 0 || (seg >= 32 && seg % 32 == 0), "segment: a multiple of 32 sources (0 = default)");
+    HGB_ARG(rows_per_tile >= 0 && rows_per_tile <= 4096 && order_weight >= 0 && order_weight <= 4096, "rows per tile / order weight");
     h->tri_seg = seg;
+    h->tri_rows = rows_per_tile;
+    h->tri_weight = order_weight;
     return HGB_OK;
 }
 
@@ -374,7 +392,8 @@ int hgb_nbody_describe(const hgb_nbody *h, char *buf, int capacity) {
     char kern[160];
     const bool fast = h->mode == HGB_NBODY_FAST;
     if (sym_applies(h) && tri_variant(h->sym)) {
-        snprintf(kern, sizeof kern, "nbody_tri_kernel<%d> seg=%d", h->sym % 10, h->tri_seg > 0 ? h->tri_seg : kTriDefaultSeg);
+        snprintf(kern, sizeof kern, "nbody_tri_kernel<%d> seg=%d rows=%d", h->sym % 10, h->tri_seg > 0 ? h->tri_seg : kTriDefaultSeg,
+                 h->tri_rows > 0 ? h->tri_rows : kTriDefaultRows);
     } else if (sym_applies(h)) {
         snprintf(kern, sizeof kern, "nbody_sym_kernel<%d,%d,%d>", h->sym / 100, h->sym / 10 % 10, h->sym % 10);
     } else {

@@ -197,9 +197,10 @@ nbody_tri_kernel(const __grid_constant__ TriArgs a) {
         const int2 bk = a.tiles[ti];
         const int I = bk.x * a.tr + r, k = bk.y;
         if (I >= a.T) continue;
+        const int i0 = 32 * I, K = i0 / a.seg;            // K = the row's last item
+        if (k > K) continue;                              // this row ends before segment k
         const long long it0 = now();
-        const int i0 = 32 * I;
-        const bool last_item = k == bk.x;                 // floor(32 I / seg) == b: this item ends the row
+        const bool last_item = k == K;
         const int j_begin = k * a.seg, j_end = last_item ? i0 : (k + 1) * a.seg;
         const int cnt = min(32, a.n - i0);                // valid targets of the row (32 except in the last row)
         const bool final_row = I == a.T - 1;
@@ -254,19 +255,35 @@ nbody_tri_kernel(const __grid_constant__ TriArgs a) {
             constexpr bool ALLV = decltype(allv)::value;
             const int chunk0 = j_begin >> 5, nchunks = (j_end - j_begin) >> 5;
             if (nchunks <= 0) return;
-            double fx = sx[j_begin + lane], fy = sy[j_begin + lane], fz = sz[j_begin + lane];   // next chunk's positions
-            ulonglong2 cw[4];                                                                 // chain words in flight
+            // positions: chunk 0 straight into ring slot 0, chunk ch+1 into the other slot at the start of
+            // chunk ch (from registers loaded one chunk earlier), so that the sources of the NEXT minitile can
+            // always be fetched from shared memory before the current one is finished
+            ring[lane] = sx[j_begin + lane]; ring[32 + lane] = sy[j_begin + lane]; ring[64 + lane] = sz[j_begin + lane];
+            double fx = 0.0, fy = 0.0, fz = 0.0;                       // positions of chunk ch+1
+            if (nchunks > 1) { const int g = j_begin + 32 + lane; fx = sx[g]; fy = sy[g]; fz = sz[g]; }
+            ulonglong2 cw[2];                                          // chain words in flight: two minitiles ahead
+            cw[0] = ll_load(a.ll + word_index(chunk0, 0));
+            cw[1] = ll_load(a.ll + word_index(chunk0, 1));
+            __syncwarp();
+            double xj[8], yj[8], zj[8];
+            auto fetch_sources = [&](const double *slot, int q) {
 #pragma unroll
-            for (int q = 0; q < 4; ++q) cw[q] = ll_load(a.ll + word_index(chunk0, q));
+                for (int u = 0; u < 8; u += 2) {
+                    const double2 x2 = *reinterpret_cast<const double2 *>(slot + q * 8 + u);
+                    const double2 y2 = *reinterpret_cast<const double2 *>(slot + 32 + q * 8 + u);
+                    const double2 z2 = *reinterpret_cast<const double2 *>(slot + 64 + q * 8 + u);
+                    xj[u] = x2.x; xj[u + 1] = x2.y; yj[u] = y2.x; yj[u + 1] = y2.y; zj[u] = z2.x; zj[u + 1] = z2.y;
+                }
+            };
+            fetch_sources(ring, 0);
             double chain = 0.0;
 #pragma unroll 1
             for (int ch = 0; ch < nchunks; ++ch) {
-                double *slot = ring + (ch & 1) * 96;
-                slot[lane] = fx; slot[32 + lane] = fy; slot[64 + lane] = fz;
-                __syncwarp();
-                if (ch + 1 < nchunks) {
-                    const int g = j_begin + 32 * (ch + 1) + lane;
-                    fx = sx[g]; fy = sy[g]; fz = sz[g];
+                const double *slot = ring + (ch & 1) * 96;
+                double *other = ring + ((ch + 1) & 1) * 96;
+                if (ch + 1 < nchunks) {   // the other slot was last read during chunk ch-1
+                    other[lane] = fx; other[32 + lane] = fy; other[64 + lane] = fz;
+                    if (ch + 2 < nchunks) { const int g = j_begin + 32 * (ch + 2) + lane; fx = sx[g]; fy = sy[g]; fz = sz[g]; }
                 }
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
@@ -274,31 +291,28 @@ nbody_tri_kernel(const __grid_constant__ TriArgs a) {
                     const bool have_prev = ch > 0 || q > 0;
                     const int pch = q > 0 ? ch : ch - 1, pq = (q + 3) & 3;       // the previous minitile
                     if (have_prev) {
-                        chain = wait_word(cw[pq], chunk0 + pch, pq);
-                        if (pch + 1 < nchunks) cw[pq] = ll_load(a.ll + word_index(chunk0 + pch + 1, pq));   // four minitiles ahead
+                        chain = wait_word(cw[pq & 1], chunk0 + pch, pq);
+                        const int nch = q < 3 ? ch : ch + 1, nq = (q + 1) & 3;    // the one after this: two ahead of pq
+                        if (nch < nchunks) cw[pq & 1] = ll_load(a.ll + word_index(chunk0 + nch, nq));
                     }
-                    double xj[8], yj[8], zj[8], vx[8], vy[8], vz[8];
-#pragma unroll
-                    for (int u = 0; u < 8; u += 2) {
-                        const double2 x2 = *reinterpret_cast<const double2 *>(slot + q * 8 + u);
-                        const double2 y2 = *reinterpret_cast<const double2 *>(slot + 32 + q * 8 + u);
-                        const double2 z2 = *reinterpret_cast<const double2 *>(slot + 64 + q * 8 + u);
-                        xj[u] = x2.x; xj[u + 1] = x2.y; yj[u] = y2.x; yj[u + 1] = y2.y; zj[u] = z2.x; zj[u + 1] = z2.y;
-                    }
+                    double vx[8], vy[8], vz[8];
                     const double *col = tb + ((q + 1) & 1) * 24 * kTbPitch + col_lane * kTbPitch;   // buffer of minitile (ch,q)-1
                     forces_and_column<ALLV>(px, py, pz, xj, yj, zj, vx, vy, vz, key, col, chain, cnt);
-                    if (have_prev) publish(chunk0 + pch, pq, chain);
+                    // the sources of the next minitile (their latency hides under the row pass)
+                    if (q < 3) fetch_sources(slot, q + 1);
+                    else if (ch + 1 < nchunks) fetch_sources(other, 0);
                     double *mine = tb + (q & 1) * 24 * kTbPitch + lane;
 #pragma unroll
                     for (int u = 0; u < 8; ++u) {   // row pass: sources ascending, the target's order
                         ax = __dadd_rn(ax, vx[u]); ay = __dadd_rn(ay, vy[u]); az = __dadd_rn(az, vz[u]);
                         mine[u * kTbPitch] = vx[u]; mine[(8 + u) * kTbPitch] = vy[u]; mine[(16 + u) * kTbPitch] = vz[u];
                     }
-                    __syncwarp();   // column lanes read these values during the next minitile
+                    if (have_prev) publish(chunk0 + pch, pq, chain);
+                    __syncwarp();   // column lanes read these values during the next minitile; ring slot hand-over
                 }
             }
-            // column pass of the segment's last minitile (chunk nchunks-1, minitile 3: buffer 1)
-            chain = wait_word(cw[3], chunk0 + nchunks - 1, 3);
+            // column pass of the segment's last minitile (chunk nchunks-1, minitile 3: buffer 1, word in cw[1])
+            chain = wait_word(cw[1], chunk0 + nchunks - 1, 3);
             const double *col = tb + 24 * kTbPitch + col_lane * kTbPitch;
 #pragma unroll
             for (int tcol = 0; tcol < 16; ++tcol) {

@@ -70,9 +70,10 @@ class NBody:
         check(lib().hgb_nbody_set_symmetric(self._h, int(variant), int(min_n)))
         return self
 
-    def segment(self, seg=0):
-        """sources per segment of the second-generation pair-symmetric kernel (multiple of 32; 0 = default)"""
-        check(lib().hgb_nbody_set_segment(self._h, int(seg)))
+    def segment(self, seg=0, rows=0, weight=0):
+        """schedule of the second-generation pair-symmetric kernel: sources per item (multiple of 32), rows
+        per tile, weight of the segment index in the ticket order (0 = default each)"""
+        check(lib().hgb_nbody_set_segment(self._h, int(seg), int(rows), int(weight)))
         return self
 
     def describe(self):

@@ -100,10 +100,12 @@ int hgb_nbody_set_symmetric(hgb_nbody *h, int variant, int min_n);
 /* Variants 2000 + C (C = 1..3 CTAs per SM; 2 = 2002; 2010 + C: with clock64 span counters) select the
  * second-generation pair-symmetric kernel (csrc/nbody_tri.cuh): forces evaluated per 32 x 8 minitile, the
  * ordered accumulation decoupled from them (row pass in registers, column pass through a shared-memory
- * transpose), rows cut into segments of `seg` sources (hgb_nbody_set_segment; 0 = 8192).  It also runs on
- * single-process multi-GPU handles with HGB_EXCHANGE_P2P: super-rows of targets are dealt over the GPUs,
- * the chain words cross NVLink as tagged stores, the last row broadcasts the finished sums. */
-int hgb_nbody_set_segment(hgb_nbody *h, int seg);
+ * transpose), rows cut into segments.  hgb_nbody_set_segment tunes its schedule: `seg` sources per item
+ * (multiple of 32), `rows_per_tile` rows whose items are handed out together, `order_weight` of the segment
+ * index in the ticket order (0 = default each: 8192, 16, 16).  It also runs on single-process multi-GPU
+ * handles with HGB_EXCHANGE_P2P: tile-rows of targets are dealt over the GPUs, the chain words cross NVLink
+ * as tagged stores, the last row broadcasts the finished sums (no position exchange). */
+int hgb_nbody_set_segment(hgb_nbody *h, int seg, int rows_per_tile, int order_weight);
 /* the variant hgb_nbody_step will use on this handle as configured now (0: the standard kernel) */
 int hgb_nbody_symmetric(const hgb_nbody *h);
 /* "<kernel> | <how targets/pairs are spread over the GPUs>" of the next hgb_nbody_step on this handle
@@ -146,6 +148,12 @@ int hgb_nbody_pairwise(const double *p1, const double *p2_aos, int count, double
 int hgb_selftest_inv_sqrt(unsigned long long count, unsigned long long seed,
                           unsigned long long *mismatches, double *first_bad);
 
+/* convolution arithmetic modes */
+#define HGB_CONV_EXACT 0 /* bit-identical to the reference: one multiply and one add per tap, row-major tap order */
+#define HGB_CONV_FAST 1  /* one fused multiply-add per tap (same order): floating-point images only, <= 1e-12
+                          * relative to the reference after 10 iterations, not bit-identical; an image whose
+                          * pixels are all integer-valued keeps the EXACT kernels (it is classified at upload) */
+
 /* ---- convolution: drop-in --------------------------------------------- */
 /*
  * Replaces  void run_on_padded_image(ImageWithPadding **padded_img, Image *kernel,
@@ -165,12 +173,18 @@ int hgb_selftest_inv_sqrt(unsigned long long count, unsigned long long seed,
  */
 int hgb_conv_run(double *cur, double *prev, int inner_w, int inner_h, int padding,
                  const double *kernel, int kw, int kh, int iterations, int ngpus);
+/* arithmetic mode of hgb_conv_run (default HGB_CONV_EXACT; env HGB_CONV_FAST=1 selects FAST) */
+int hgb_set_conv_mode(int mode);
 
 /* ---- convolution: device-resident ------------------------------------- */
 typedef struct hgb_conv hgb_conv;
 int hgb_conv_create(hgb_conv **out, int inner_w, int inner_h, int padding, int ngpus);
 int hgb_conv_create_rank(hgb_conv **out, int inner_w, int inner_h, int padding);
 int hgb_conv_set_kernel(hgb_conv *h, const double *kernel, int kw, int kh);
+/* HGB_CONV_EXACT (default) or HGB_CONV_FAST; FAST must be chosen before the upload.  hgb_conv_mode_in_effect
+ * tells what the next step will really use (EXACT when the uploaded image was integer-valued). */
+int hgb_conv_set_mode(hgb_conv *h, int mode);
+int hgb_conv_mode_in_effect(const hgb_conv *h);
 /* variant bit 0: generic kernel instead of the specialised one; bit 1: no boundary/interior overlap
  * in the multi-GPU step; bit 2: no two-iterations-per-pass kernel for 3x3; bit 3: that kernel with 4 columns per thread instead
  * of 2; band_rows: output rows

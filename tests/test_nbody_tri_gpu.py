@@ -19,10 +19,10 @@ def sha(a):
     return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
 
 
-def tri_step(hgb, pos, iters, variant=2, seg=0, ngpus=1, want_prev=False):
+def tri_step(hgb, pos, iters, variant=2, seg=0, ngpus=1, want_prev=False, rows=0, weight=0):
     kind = hgb.EXCHANGE_P2P if ngpus > 1 else hgb.EXCHANGE_NCCL
     with hgb.nbody.NBody(pos.shape[0], ngpus=ngpus, exchange=kind) as nb:
-        nb.symmetric(variant, 0).segment(seg).upload(pos)
+        nb.symmetric(variant, 0).segment(seg, rows, weight).upload(pos)
         assert hgb.lib().hgb_nbody_symmetric(nb._h) >= 2001
         nb.step(iters)
         return nb.download(want_prev=want_prev)
@@ -47,14 +47,15 @@ def test_tri_ragged_sizes_vs_oracle(hgb, n, iters, seg):
 
 
 @pytest.mark.parametrize("variant", [2001, 2002, 2003, 2011, 2012, 2013])
-@pytest.mark.parametrize("seg", [64, 2048, 0])
-def test_tri_every_variant_gives_the_same_bits(hgb, variant, seg):
+@pytest.mark.parametrize("seg,rows,weight", [(64, 1, 1), (64, 3, 2), (2048, 16, 16), (96, 256, 1), (0, 0, 0)])
+def test_tri_every_variant_and_schedule_gives_the_same_bits(hgb, variant, seg, rows, weight):
     from oracle import port
     for n in (3000, 777):
         pos = synth.plummer(n, seed=7)
         want = np.zeros_like(pos)
         port.nbody_step_range(pos, want, 0, n)
-        assert np.array_equal(tri_step(hgb, pos, 1, variant, seg), want), (variant, seg, n)
+        got = tri_step(hgb, pos, 1, variant, seg, rows=rows, weight=weight)
+        assert np.array_equal(got, want), (variant, seg, rows, weight, n)
 
 
 @pytest.mark.parametrize("name,gen,n,iters", [("uniform", synth.uniform_cube, 2049, 10),
@@ -106,7 +107,7 @@ def test_tri_many_steps_and_epoch_wrap(hgb):
     want4, _ = oracle_run(pos, 4)
     want1, _ = oracle_run(pos, 1)
     with hgb.nbody.NBody(n) as nb:
-        nb.symmetric(2, 0).segment(64).upload(pos)
+        nb.symmetric(2, 0).segment(64, 2, 3).upload(pos)
         nb.step(37)
         nb.upload(pos)
         nb.step(4)
@@ -138,8 +139,9 @@ def test_tri_rows_dealt_over_gpus_are_bit_identical(hgb, monkeypatch, n, iters, 
     sample = np.random.default_rng(n).choice(n, size=min(n, 96), replace=False).astype(np.int32)
     assert np.array_equal(one_cur[sample], port.nbody_accel_subset(one_prev, sample))
     for g in counts:
-        cur, prev = tri_step(hgb, pos, iters, seg=seg, ngpus=g, want_prev=True)
-        assert np.array_equal(cur, one_cur) and np.array_equal(prev, one_prev), g
+        for rows in (0, 1, 5):
+            cur, prev = tri_step(hgb, pos, iters, seg=seg, ngpus=g, want_prev=True, rows=rows, weight=rows)
+            assert np.array_equal(cur, one_cur) and np.array_equal(prev, one_prev), (g, rows)
 
 
 def test_tri_64k_plummer_all_bodies_equal_the_standard_kernel(hgb):

@@ -1,7 +1,7 @@
 """CPU model of the second-generation pair-symmetric nbody schedule (csrc/nbody_tri.cuh).
 
 Test infrastructure: it mirrors the index logic of `nbody_tri_kernel` -- rows of 32 targets, segments,
-tiles in anti-diagonal ticket order dealt over `world` GPUs, 32 x 8 minitiles with a row pass (targets add
+tiles of `rows` rows in key order (tile-row + weight * segment) dealt over `world` GPUs, 32 x 8 minitiles with a row pass (targets add
 their 8 sources in order) and a column pass (each source's chain subtracts the 32 targets in order), the
 row's own triangle with chain seeds, tagged hand-off words between rows and between the items of a row,
 the final row's broadcast -- with Python floats (IEEE binary64, one rounding per operator).  Items are
@@ -17,12 +17,12 @@ MT = 8
 
 
 class TriModel:
-    def __init__(self, pos, seg=64, world=1):
-        assert seg % 32 == 0
-        self.pos, self.n, self.seg, self.world = pos, len(pos), seg, world
+    def __init__(self, pos, seg=64, world=1, rows=2, weight=3):
+        assert seg % 32 == 0 and rows >= 1 and weight >= 1
+        self.pos, self.n, self.seg, self.world, self.weight = pos, len(pos), seg, world, weight
         self.T = (self.n + 31) // 32
-        self.tr = seg // 32
-        self.TS = (self.T + self.tr - 1) // self.tr
+        self.tr = rows                                    # rows per tile
+        self.TS = (self.T + self.tr - 1) // self.tr       # tile-rows
         npad = self.T * 32
         self.x = [p[0] for p in pos] + [0.0] * (npad - self.n)
         self.y = [p[1] for p in pos] + [0.0] * (npad - self.n)
@@ -33,23 +33,24 @@ class TriModel:
         self.items = 0
 
     def plan(self, index):
-        """tiles of shard `index` in ticket order (hgb_nbody.cu tri_plan)"""
+        """tiles of shard `index` in ticket order (hgb_nbody.cu tri_plan): key b + weight * k, then k"""
         tiles = []
-        for d in range(2 * (self.TS - 1) + 1):
-            for k in range(max(0, d - self.TS + 1), d // 2 + 1):
-                b = d - k
-                if b % self.world == index:
-                    tiles.append((b, k))
-        return tiles
+        for b in range(index, self.TS, self.world):
+            last_row = min(self.T - 1, b * self.tr + self.tr - 1)
+            for k in range(32 * last_row // self.seg + 1):
+                tiles.append(((b + self.weight * k) * 4096 + k, b, k))
+        return [(b, k) for _, b, k in sorted(tiles)]
 
     def item(self, dev, b, k, r):
         I = b * self.tr + r
         if I >= self.T:
             return
-        self.items += 1
         n, i0 = self.n, 32 * I
-        last_item = k == b
-        assert (i0 // self.seg) == b                      # floor(32 I / seg) == b for every row of super-row b
+        K = i0 // self.seg                                # the row's last item
+        if k > K:
+            return                                        # this row ends before segment k
+        self.items += 1
+        last_item = k == K
         j_begin, j_end = k * self.seg, (i0 if last_item else (k + 1) * self.seg)
         cnt = min(32, n - i0)
         final_row = I == self.T - 1
@@ -102,16 +103,14 @@ class TriModel:
 
     def step(self):
         plans = [self.plan(g) for g in range(self.world)]
-        # global anti-diagonal order (b + k ascending, k ascending inside): its restriction to a shard is
-        # that shard's ticket order
-        order = sorted(((b + k, k, b, g) for g in range(self.world) for (b, k) in plans[g]))
+        # global key order: its restriction to a shard is that shard's ticket order
+        order = sorted((((b + self.weight * k) * 4096 + k, b, k, g) for g in range(self.world) for (b, k) in plans[g]))
         seen = set()
-        for _, k, b, g in order:
+        for _, b, k, g in order:
             assert b % self.world == g and (b, k) not in seen
             seen.add((b, k))
             for r in range(self.tr):
                 self.item(g, b, k, r)
-        assert len(seen) == self.TS * (self.TS + 1) // 2
         out = []
         for g in range(self.world):                       # every GPU holds the finished sums
             res = []
