@@ -144,6 +144,37 @@ __device__ __forceinline__ void forces_and_column(double px, double py, double p
     static_assert(2 + 2 + 12 == 16, "16 column pairs = 32 targets");
 }
 
+// ---- cold paths, out of line: the hot loop must stay small (a 2^17-body profile of the first version showed
+// one "no instruction" stall per issued instruction: the unrolled cold code had pushed the loop out of the
+// instruction cache) ------------------------------------------------------------------------------------
+// raise flag ctl[which] (1: operand out of range, 2: step abandoned) on every GPU
+__device__ __noinline__ void tri_raise(const TriArgs &a, int which) {
+    for (int p = 0; p < a.npeers; ++p) *reinterpret_cast<volatile int *>(a.ctl_all[p] + which) = 1;
+    __threadfence_system();
+}
+// the last row of the step: its words are the finished sums and go to every GPU
+__device__ __noinline__ void tri_publish_all(const TriArgs &a, size_t at, ulonglong2 w) {
+    for (int p = 0; p < a.npeers; ++p) ll_store(a.ll_all[p] + at, w);
+}
+// poll one tagged word until its tag shows (every lane of the warp calls this together and all leave
+// together); a poll that outlasts the spin limit raises the abort flag everywhere, after which nobody waits
+// any more (results are garbage, the host reports the failure).  Returns the clock ticks spent.
+__device__ __noinline__ ulonglong2 tri_poll(const TriArgs &a, const ulonglong2 *q, unsigned tag, int &dead,
+                                            unsigned ns, long long &spent) {
+    const long long t0 = clock64();
+    ulonglong2 w = make_ulonglong2(0, 0);
+    while (!dead) {
+        w = ll_load(q);
+        if (__all_sync(0xffffffffu, ll_ok(w, tag))) break;
+        bool g = *reinterpret_cast<volatile int *>(a.ctl + 2) != 0;
+        if (!g && clock64() - t0 > a.spin_limit) { tri_raise(a, 2); g = true; }
+        dead = __any_sync(0xffffffffu, g);
+        __nanosleep(ns);
+    }
+    spent += clock64() - t0;
+    return w;
+}
+
 // CTAS resident CTAs per SM (register budget).  PROF: lane 0 of every warp accumulates clock64 spans
 // (waits for chain words, waits for row accumulators, whole items, the diagonal triangles) in ctl[8..].
 template <int CTAS, bool PROF = false>
@@ -159,34 +190,13 @@ nbody_tri_kernel(const __grid_constant__ TriArgs a) {
     const int col_lane = lane < 24 ? lane : 23;                       // lanes 24..31 shadow lane 23 and never publish
     const int cc = col_lane >> 3, cu = col_lane & 7;                  // component, source within the minitile
     unsigned key = 0;
-    bool dead = false;                                                // the step was abandoned (spin limit)
-    long long t_chain = 0, t_racc = 0, t_item = 0, t_diag = 0, n_items = 0;
-    auto now = [] { return PROF ? clock64() : 0ll; };
-
-    // a poll that has lasted too long raises the abort flag everywhere; everyone then runs to the end
-    // without waiting (results are garbage, the host reports the failure).  Warp-uniform: every lane calls
-    // it from the same poll loop and all leave together.
-    auto give_up = [&](long long t0) -> bool {
-        bool g = dead;
-        if (!g && *reinterpret_cast<volatile int *>(a.ctl + 2) != 0) g = true;
-        if (!g && clock64() - t0 > a.spin_limit) {
-            for (int p = 0; p < a.npeers; ++p) *reinterpret_cast<volatile int *>(a.ctl_all[p] + 2) = 1;
-            g = true;
-        }
-        dead = __any_sync(FULL, g);
-        return dead;
-    };
-    // an operand left the range of the branch-free IEEE sequences (never for sane finite positions): the
-    // flag is raised on every GPU BEFORE anything computed from it is published, so whoever sees the
-    // final words of the step also sees the flag, and the ordinary kernel redoes the step everywhere
+    // only the out-of-line poll ever takes the address of these (they may live in local memory; the hot
+    // loop never touches them)
+    int dead = 0;                                                     // the step was abandoned (spin limit)
+    long long t_chain = 0, t_racc = 0;
     bool raised = false;
-    auto check_range = [&]() {
-        if (!raised && __any_sync(FULL, key >= kRangeLimit)) {
-            for (int p = 0; p < a.npeers; ++p) *reinterpret_cast<volatile int *>(a.ctl_all[p] + 1) = 1;
-            __threadfence_system();
-            raised = true;
-        }
-    };
+    long long t_item = 0, t_diag = 0, n_items = 0;
+    auto now = [] { return PROF ? clock64() : 0ll; };
 
     for (;;) {
         int ticket = 0;
@@ -206,113 +216,89 @@ nbody_tri_kernel(const __grid_constant__ TriArgs a) {
         const bool final_row = I == a.T - 1;
         const unsigned want_tag = a.epoch_tag | (unsigned)I;          // written by row I-1
         const unsigned my_tag = a.epoch_tag | (unsigned)(I + 1);
-        ulonglong2 *pub = (r == a.tr - 1) ? a.ll_down : a.ll;         // row I+1 is the next super-row's first row
+        ulonglong2 *pub = (r == a.tr - 1) ? a.ll_down : a.ll;         // row I+1 is the next tile-row's first row
 
         const double px = sx[i0 + lane], py = sy[i0 + lane], pz = sz[i0 + lane];
         double ax = 0.0, ay = 0.0, az = 0.0;
         if (k > 0) {   // the row's sums so far, left by item (I, k-1)
             const ulonglong2 *q = a.racc + (size_t)I * 96 + lane;
             const unsigned tag = a.epoch_tag | (unsigned)k;
-            const long long w0 = clock64();
-            ulonglong2 wx = ll_load(q), wy = ll_load(q + 32), wz = ll_load(q + 64);
-            while (!__all_sync(FULL, ll_ok(wx, tag) && ll_ok(wy, tag) && ll_ok(wz, tag))) {
-                if (give_up(w0)) break;
-                __nanosleep(100);
-                wx = ll_load(q); wy = ll_load(q + 32); wz = ll_load(q + 64);
-            }
-            ax = ll_unpack(wx); ay = ll_unpack(wy); az = ll_unpack(wz);
-            if (PROF) t_racc += clock64() - w0;
+            ax = ll_unpack(tri_poll(a, q, tag, dead, 100, t_racc));
+            ay = ll_unpack(tri_poll(a, q + 32, tag, dead, 100, t_racc));
+            az = ll_unpack(tri_poll(a, q + 64, tag, dead, 100, t_racc));
         }
 
-        // chain word of (minitile mt of chunk ch) for this column lane
-        auto word_index = [&](int chunk, int mt) { return (size_t)chunk * 96 + cc * 32 + mt * 8 + cu; };
-        auto publish = [&](int chunk, int mt, double chain) {
-            check_range();
+        // An operand left the range of the branch-free IEEE sequences (never for sane finite positions): the
+        // flag is raised on every GPU BEFORE anything computed from it is published, so whoever sees the
+        // final words of the step also sees the flag, and the ordinary kernel redoes the step everywhere.
+        auto publish = [&](size_t at, double chain) {
+            if (!raised && __any_sync(FULL, key >= kRangeLimit)) { tri_raise(a, 1); raised = true; }
             if (lane >= 24) return;
             const ulonglong2 w = ll_pack(chain, my_tag);
-            const size_t at = word_index(chunk, mt);
-            if (final_row) {
-                for (int p = 0; p < a.npeers; ++p) ll_store(a.ll_all[p] + at, w);
-            } else {
-                ll_store(pub + at, w);
-            }
+            if (final_row) tri_publish_all(a, at, w);
+            else ll_store(pub + at, w);
         };
-        auto wait_word = [&](ulonglong2 &w, int chunk, int mt) -> double {
-            if (!__all_sync(FULL, ll_ok(w, want_tag))) {
-                const long long w0 = clock64();
-                const ulonglong2 *q = a.ll + word_index(chunk, mt);
-                do {
-                    if (give_up(w0)) break;
-                    __nanosleep(40);
-                    w = ll_load(q);
-                } while (!__all_sync(FULL, ll_ok(w, want_tag)));
-                if (PROF) t_chain += clock64() - w0;
-            }
+        auto wait_word = [&](ulonglong2 w, size_t at) -> double {
+            if (!__all_sync(FULL, ll_ok(w, want_tag))) w = tri_poll(a, a.ll + at, want_tag, dead, 40, t_chain);
             return ll_unpack(w);
         };
 
         auto lower = [&](auto allv) {
             constexpr bool ALLV = decltype(allv)::value;
-            const int chunk0 = j_begin >> 5, nchunks = (j_end - j_begin) >> 5;
+            const int nchunks = (j_end - j_begin) >> 5, M = 4 * nchunks;
             if (nchunks <= 0) return;
+            // chain word of minitile m of this item for this column lane
+            const size_t w0 = (size_t)(j_begin >> 5) * 96 + cc * 32 + cu;
+            auto word_at = [&](int m) { return w0 + (size_t)(m >> 2) * 96 + (m & 3) * 8; };
             // positions: chunk 0 straight into ring slot 0, chunk ch+1 into the other slot at the start of
             // chunk ch (from registers loaded one chunk earlier), so that the sources of the NEXT minitile can
             // always be fetched from shared memory before the current one is finished
             ring[lane] = sx[j_begin + lane]; ring[32 + lane] = sy[j_begin + lane]; ring[64 + lane] = sz[j_begin + lane];
             double fx = 0.0, fy = 0.0, fz = 0.0;                       // positions of chunk ch+1
             if (nchunks > 1) { const int g = j_begin + 32 + lane; fx = sx[g]; fy = sy[g]; fz = sz[g]; }
-            ulonglong2 cw[2];                                          // chain words in flight: two minitiles ahead
-            cw[0] = ll_load(a.ll + word_index(chunk0, 0));
-            cw[1] = ll_load(a.ll + word_index(chunk0, 1));
+            // chain words in flight: `wa` belongs to the minitile whose column pass comes next, `wb` to the one after
+            ulonglong2 wa = make_ulonglong2(0, 0), wb = ll_load(a.ll + word_at(0));
             __syncwarp();
             double xj[8], yj[8], zj[8];
-            auto fetch_sources = [&](const double *slot, int q) {
+            auto fetch_sources = [&](const double *from) {
 #pragma unroll
                 for (int u = 0; u < 8; u += 2) {
-                    const double2 x2 = *reinterpret_cast<const double2 *>(slot + q * 8 + u);
-                    const double2 y2 = *reinterpret_cast<const double2 *>(slot + 32 + q * 8 + u);
-                    const double2 z2 = *reinterpret_cast<const double2 *>(slot + 64 + q * 8 + u);
+                    const double2 x2 = *reinterpret_cast<const double2 *>(from + u);
+                    const double2 y2 = *reinterpret_cast<const double2 *>(from + 32 + u);
+                    const double2 z2 = *reinterpret_cast<const double2 *>(from + 64 + u);
                     xj[u] = x2.x; xj[u + 1] = x2.y; yj[u] = y2.x; yj[u + 1] = y2.y; zj[u] = z2.x; zj[u + 1] = z2.y;
                 }
             };
-            fetch_sources(ring, 0);
+            fetch_sources(ring);
             double chain = 0.0;
 #pragma unroll 1
-            for (int ch = 0; ch < nchunks; ++ch) {
-                const double *slot = ring + (ch & 1) * 96;
-                double *other = ring + ((ch + 1) & 1) * 96;
-                if (ch + 1 < nchunks) {   // the other slot was last read during chunk ch-1
+            for (int m = 0; m < M; ++m) {
+                const int q = m & 3, ch = m >> 2;
+                if (q == 0 && ch + 1 < nchunks) {   // the other ring slot was last read during chunk ch-1
+                    double *other = ring + ((ch + 1) & 1) * 96;
                     other[lane] = fx; other[32 + lane] = fy; other[64 + lane] = fz;
                     if (ch + 2 < nchunks) { const int g = j_begin + 32 * (ch + 2) + lane; fx = sx[g]; fy = sy[g]; fz = sz[g]; }
                 }
+                // minitile m: forces + row pass, fused with the column pass of minitile m-1
+                if (m > 0) chain = wait_word(wa, word_at(m - 1));
+                wa = wb;                                                // word of minitile m: consumed next iteration
+                if (m + 1 < M) wb = ll_load(a.ll + word_at(m + 1));     // two minitiles ahead of its use
+                double vx[8], vy[8], vz[8];
+                const double *col = tb + ((m + 1) & 1) * 24 * kTbPitch + col_lane * kTbPitch;   // buffer of minitile m-1
+                forces_and_column<ALLV>(px, py, pz, xj, yj, zj, vx, vy, vz, key, col, chain, cnt);
+                // the sources of the next minitile (their latency hides under the row pass)
+                if (m + 1 < M) fetch_sources(ring + (((m + 1) >> 2) & 1) * 96 + ((m + 1) & 3) * 8);
+                double *mine = tb + (m & 1) * 24 * kTbPitch + lane;
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    // minitile (ch, q): forces + row pass; column pass of the minitile before it
-                    const bool have_prev = ch > 0 || q > 0;
-                    const int pch = q > 0 ? ch : ch - 1, pq = (q + 3) & 3;       // the previous minitile
-                    if (have_prev) {
-                        chain = wait_word(cw[pq & 1], chunk0 + pch, pq);
-                        const int nch = q < 3 ? ch : ch + 1, nq = (q + 1) & 3;    // the one after this: two ahead of pq
-                        if (nch < nchunks) cw[pq & 1] = ll_load(a.ll + word_index(chunk0 + nch, nq));
-                    }
-                    double vx[8], vy[8], vz[8];
-                    const double *col = tb + ((q + 1) & 1) * 24 * kTbPitch + col_lane * kTbPitch;   // buffer of minitile (ch,q)-1
-                    forces_and_column<ALLV>(px, py, pz, xj, yj, zj, vx, vy, vz, key, col, chain, cnt);
-                    // the sources of the next minitile (their latency hides under the row pass)
-                    if (q < 3) fetch_sources(slot, q + 1);
-                    else if (ch + 1 < nchunks) fetch_sources(other, 0);
-                    double *mine = tb + (q & 1) * 24 * kTbPitch + lane;
-#pragma unroll
-                    for (int u = 0; u < 8; ++u) {   // row pass: sources ascending, the target's order
-                        ax = __dadd_rn(ax, vx[u]); ay = __dadd_rn(ay, vy[u]); az = __dadd_rn(az, vz[u]);
-                        mine[u * kTbPitch] = vx[u]; mine[(8 + u) * kTbPitch] = vy[u]; mine[(16 + u) * kTbPitch] = vz[u];
-                    }
-                    if (have_prev) publish(chunk0 + pch, pq, chain);
-                    __syncwarp();   // column lanes read these values during the next minitile; ring slot hand-over
+                for (int u = 0; u < 8; ++u) {   // row pass: sources ascending, the target's order
+                    ax = __dadd_rn(ax, vx[u]); ay = __dadd_rn(ay, vy[u]); az = __dadd_rn(az, vz[u]);
+                    mine[u * kTbPitch] = vx[u]; mine[(8 + u) * kTbPitch] = vy[u]; mine[(16 + u) * kTbPitch] = vz[u];
                 }
+                if (m > 0) publish(word_at(m - 1), chain);
+                __syncwarp();   // column lanes read these values during the next minitile; ring slot hand-over
             }
-            // column pass of the segment's last minitile (chunk nchunks-1, minitile 3: buffer 1, word in cw[1])
-            chain = wait_word(cw[1], chunk0 + nchunks - 1, 3);
+            // column pass of the segment's last minitile (M-1 is odd: buffer 1; its word is in `wa`)
+            chain = wait_word(wa, word_at(M - 1));
             const double *col = tb + 24 * kTbPitch + col_lane * kTbPitch;
 #pragma unroll
             for (int tcol = 0; tcol < 16; ++tcol) {
@@ -320,7 +306,7 @@ nbody_tri_kernel(const __grid_constant__ TriArgs a) {
                 if (ALLV || 2 * tcol < cnt) chain = __dsub_rn(chain, v.x);
                 if (ALLV || 2 * tcol + 1 < cnt) chain = __dsub_rn(chain, v.y);
             }
-            publish(chunk0 + nchunks - 1, 3, chain);
+            publish(word_at(M - 1), chain);
             __syncwarp();
         };
         if (cnt == 32) lower(std::true_type{});
@@ -358,7 +344,7 @@ nbody_tri_kernel(const __grid_constant__ TriArgs a) {
                 double chain = seed[col_lane];
                 const double *col = tb + col_lane * kTbPitch;
                 for (int i = mt * 8 + cu + 1; i < cnt; ++i) chain = __dsub_rn(chain, col[i]);
-                publish(I, mt, chain);
+                publish((size_t)I * 96 + cc * 32 + mt * 8 + cu, chain);
                 __syncwarp();
             }
             if (PROF) t_diag += now() - d0;
@@ -371,7 +357,7 @@ nbody_tri_kernel(const __grid_constant__ TriArgs a) {
         atomicAdd(c + 2, (unsigned long long)t_item); atomicAdd(c + 3, (unsigned long long)t_diag);
         atomicAdd(c + 4, (unsigned long long)n_items);
     }
-    check_range();
+    if (!raised && __any_sync(FULL, key >= kRangeLimit)) tri_raise(a, 1);
 }
 
 // buffer[i] = G * acc[i] (reference src/nbody/nbody-run.c:22-24).  acc = what the LAST row published (tag

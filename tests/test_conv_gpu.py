@@ -373,3 +373,68 @@ def test_fused_3x3_split_steps_and_special_values(hgb):
         plain = cv.download(want_prev=True)
     for a, b, c in zip(want, got, plain):
         assert a.tobytes() == b.tobytes() == c.tobytes()
+
+
+# ---- FAST mode (fused multiply-add taps): opt-in, floating-point images only ----------------------
+@pytest.mark.parametrize("w,h,kshape,it", [(300, 70, (3, 3), 10), (513, 260, (5, 5), 10), (640, 133, (7, 7), 10),
+                                           (257, 64, (3, 5), 6), (1024, 1024, (3, 3), 10), (1024, 512, (7, 7), 10)])
+def test_fast_mode_is_within_1e_12_of_the_reference_on_float_images(hgb, w, h, kshape, it):
+    """north_star tolerance for floating-point images: 1e-12 relative (max-norm) after 10 iterations;
+    the EXACT mode stays the parity path, FAST only contracts each tap's multiply-add into one FMA
+    (reference arithmetic relaxed: src/convolution/convolution-run.c:71-77)"""
+    from oracle import port
+    kh, kw = kshape
+    p = max(kh, kw) // 2
+    kern = synth.kernel_dense(max(kh, kw))[:kh, :kw].copy()
+    kern /= np.abs(kern).sum()                           # keep 10 iterations in range
+    img = synth.add_padding(synth.image_float(w, h, seed=w + h), p)
+    want_c, want_p = img.copy(), np.zeros_like(img)
+    port.conv_run(want_c, want_p, w, h, p, kern, it)
+    with hgb.convolution.Conv2D(w, h, p) as cv:
+        cv.set_mode(hgb.CONV_FAST).set_kernel(kern).upload(img)
+        assert cv.mode_in_effect() == hgb.CONV_FAST
+        cv.step(it)
+        cur, prev = cv.download(want_prev=True)
+    tol = 1e-12                                          # the stated tolerance
+    assert np.abs(cur - want_c).max() <= tol * np.abs(want_c).max()
+    assert np.abs(prev - want_p).max() <= tol * np.abs(want_p).max()
+    assert not np.array_equal(cur, want_c) or it == 0    # it really is the other arithmetic
+
+
+@pytest.mark.parametrize("k", [3, 5, 7])
+def test_fast_mode_keeps_integer_images_bit_exact(hgb, k):
+    """an integer-valued image is classified at upload and keeps the exact kernels"""
+    from oracle import port
+    w, h, p, it = 400, 90, k // 2, 5
+    kern = synth.kernel_dense(k)
+    img = synth.add_padding(synth.image_int(w, h, seed=4), p)
+    want_c, want_p = img.copy(), np.zeros_like(img)
+    port.conv_run(want_c, want_p, w, h, p, kern, it)
+    with hgb.convolution.Conv2D(w, h, p) as cv:
+        cv.set_mode(hgb.CONV_FAST).set_kernel(kern).upload(img)
+        assert cv.mode_in_effect() == hgb.CONV_EXACT
+        cv.step(it)
+        cur, prev = cv.download(want_prev=True)
+        assert np.array_equal(cur, want_c) and np.array_equal(prev, want_p)
+        img[17, 33] += 0.5                               # one non-integer pixel: a floating-point image
+        cv.upload(img)
+        assert cv.mode_in_effect() == hgb.CONV_FAST
+        with pytest.raises(hgb.HgbError):                # the mode is fixed at upload
+            hgb.convolution.Conv2D(8, 8, 1).set_kernel(synth.kernel_dense(3)).upload(np.zeros((8, 10))).set_mode(hgb.CONV_FAST)
+
+
+def test_fast_mode_row_bands_agree_with_one_gpu(hgb, monkeypatch):
+    """same arithmetic on every band: FAST over row bands is bit-identical to FAST on one GPU"""
+    counts = _gpu_counts(hgb, monkeypatch, "p2p")
+    w, h, k, p, it = 513, 1300, 3, 1, 9
+    kern = synth.kernel_dense(k) / 5.0
+    img = synth.add_padding(synth.image_float(w, h, seed=77), p)
+    with hgb.convolution.Conv2D(w, h, p, ngpus=1) as one:
+        one.set_mode(hgb.CONV_FAST).set_kernel(kern).upload(img)
+        one.step(it)
+        want = one.download()
+    for g in counts:
+        with hgb.convolution.Conv2D(w, h, p, ngpus=g) as cv:
+            cv.set_exchange(hgb.EXCHANGE_P2P).set_mode(hgb.CONV_FAST).set_kernel(kern).upload(img)
+            cv.step(it)
+            assert np.array_equal(cv.download(), want), g
