@@ -229,7 +229,7 @@ static int launch_tri_variant(const TriArgs &a, int grid, cudaStream_t st) {
 }
 
 // one step on every shard: tickets reset, wavefront kernels (all launched before any finish kernel), G*acc of
-// all n bodies from the local copy of the final words, conditional redo by the standard kernel.  Every
+// all n bodies from the final words (read from the shard that ran the last row), conditional redo by the standard kernel.  Every
 // shard ends with the complete next state: no exchange follows.
 static int launch_tri_step(hgb_nbody *h, int cur, int nxt) {
     HGB_TRY(tri_alloc(h));
@@ -264,7 +264,7 @@ static int launch_tri_step(hgb_nbody *h, int cur, int nxt) {
         a.ll = s.tri_ll[parity];
         a.ll_down = h->sh[(s.index + 1) % h->world].tri_ll[parity];   // tile-row b+1 lives on the next shard
         a.npeers = h->world;
-        for (int p = 0; p < h->world; ++p) { a.ll_all[p] = h->sh[p].tri_ll[parity]; a.ctl_all[p] = h->sh[p].tri_ctl; }
+        for (int p = 0; p < h->world; ++p) a.ctl_all[p] = h->sh[p].tri_ctl;
         a.racc = s.tri_racc; a.epoch_tag = epoch_tag; a.ctl = s.tri_ctl; a.spin_limit = kTriSpinLimit;
         const int grid = std::max(1, s.dev->sms * ctas / tri_shards_on_device(h, s));
         int rc = HGB_ERR_ARG;
@@ -284,7 +284,9 @@ static int launch_tri_step(hgb_nbody *h, int cur, int nxt) {
         // a small persistent grid: while it polls for the final words it must not crowd out a wavefront
         // kernel that shares the device (virtual shards)
         const int fgrid = std::min((h->n + 255) / 256, std::max(1, s.dev->sms / tri_shards_on_device(h, s)));
-        nbody_tri_finish_kernel<<<fgrid, 256, 0, s.dev->stream>>>(s.tri_ll[parity], h->npad, h->n,
+        // the finished sums are the words of the LAST row, in the buffer of the shard that ran it
+        const NbShard &owner = h->sh[((T - 1) / rows) % h->world];
+        nbody_tri_finish_kernel<<<fgrid, 256, 0, s.dev->stream>>>(owner.tri_ll[parity], h->npad, h->n,
                                                                  epoch_tag | (unsigned)T, s.state[nxt], s.tri_ctl,
                                                                  kTriSpinLimit);
         HGB_LAUNCHED();

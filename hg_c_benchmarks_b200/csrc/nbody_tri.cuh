@@ -26,8 +26,8 @@
 //     publishes value and flag, no fence; the "LL" scheme of collective libraries).  Row I expects
 //     tag (epoch | I), written by row I-1, and publishes with (epoch | I+1) -- into the local buffer,
 //     or into the buffer of the GPU that runs row I+1 (peer-mapped pointer: the store crosses NVLink).
-//     The last row publishes into EVERY GPU's buffer: those words are the finished accumulators, so
-//     no position exchange follows the step.
+//     The words of the last row are the finished accumulators: every GPU's finish kernel reads them from
+//     the buffer of the GPU that ran the last row (peer-mapped loads), so no position exchange follows.
 //   * Hand-off between the items of one row: the row's 32 x 3 accumulators through a tagged buffer.
 //   * Order.  Items are grouped in TILES (b, k) = the `tr` = seg/32 rows of super-row b against segment
 //     k, k <= b.  Item (I, k) needs (I, k-1) finished (row accumulators) and streams the chain words of
@@ -56,7 +56,6 @@ struct TriArgs {
     int ntiles;
     ulonglong2 *ll;           // chain words this GPU reads: [chunk of 32 sources][x, y, z][32] x 16 B
     ulonglong2 *ll_down;      // where the LAST row of a super-row publishes (buffer of the next super-row's GPU)
-    ulonglong2 *ll_all[kMaxPeers];   // every GPU's buffer: the last row of the step publishes into all of them
     int npeers;
     ulonglong2 *racc;         // row accumulators between the items of a row: [row][x, y, z][32] x 16 B
     unsigned epoch_tag;       // (launch epoch) << 21
@@ -152,10 +151,6 @@ __device__ __noinline__ void tri_raise(const TriArgs &a, int which) {
     for (int p = 0; p < a.npeers; ++p) *reinterpret_cast<volatile int *>(a.ctl_all[p] + which) = 1;
     __threadfence_system();
 }
-// the last row of the step: its words are the finished sums and go to every GPU
-__device__ __noinline__ void tri_publish_all(const TriArgs &a, size_t at, ulonglong2 w) {
-    for (int p = 0; p < a.npeers; ++p) ll_store(a.ll_all[p] + at, w);
-}
 // poll one tagged word until its tag shows (every lane of the warp calls this together and all leave
 // together); a poll that outlasts the spin limit raises the abort flag everywhere, after which nobody waits
 // any more (results are garbage, the host reports the failure).  Returns the clock ticks spent.
@@ -194,7 +189,6 @@ nbody_tri_kernel(const __grid_constant__ TriArgs a) {
     // loop never touches them)
     int dead = 0;                                                     // the step was abandoned (spin limit)
     long long t_chain = 0, t_racc = 0;
-    bool raised = false;
     long long t_item = 0, t_diag = 0, n_items = 0;
     auto now = [] { return PROF ? clock64() : 0ll; };
 
@@ -216,7 +210,8 @@ nbody_tri_kernel(const __grid_constant__ TriArgs a) {
         const bool final_row = I == a.T - 1;
         const unsigned want_tag = a.epoch_tag | (unsigned)I;          // written by row I-1
         const unsigned my_tag = a.epoch_tag | (unsigned)(I + 1);
-        ulonglong2 *pub = (r == a.tr - 1) ? a.ll_down : a.ll;         // row I+1 is the next tile-row's first row
+        // row I+1 is the next tile-row's first row; the last row of the step keeps its words (the finished sums) here
+        ulonglong2 *pub = (r == a.tr - 1 && !final_row) ? a.ll_down : a.ll;
 
         const double px = sx[i0 + lane], py = sy[i0 + lane], pz = sz[i0 + lane];
         double ax = 0.0, ay = 0.0, az = 0.0;
@@ -229,17 +224,16 @@ nbody_tri_kernel(const __grid_constant__ TriArgs a) {
         }
 
         // An operand left the range of the branch-free IEEE sequences (never for sane finite positions): the
-        // flag is raised on every GPU BEFORE anything computed from it is published, so whoever sees the
-        // final words of the step also sees the flag, and the ordinary kernel redoes the step everywhere.
-        auto publish = [&](size_t at, double chain) {
-            if (!raised && __any_sync(FULL, key >= kRangeLimit)) { tri_raise(a, 1); raised = true; }
-            if (lane >= 24) return;
-            const ulonglong2 w = ll_pack(chain, my_tag);
-            if (final_row) tri_publish_all(a, at, w);
-            else ll_store(pub + at, w);
+        // flag is raised on every GPU BEFORE the last words computed from it are published, so whoever has
+        // seen all final words of the step also sees the flag, and the ordinary kernel redoes the step.
+        auto check_range = [&]() {
+            if (__any_sync(FULL, key >= kRangeLimit)) { tri_raise(a, 1); key = 0; }
         };
-        auto wait_word = [&](ulonglong2 w, size_t at) -> double {
-            if (!__all_sync(FULL, ll_ok(w, want_tag))) w = tri_poll(a, a.ll + at, want_tag, dead, 40, t_chain);
+        auto publish = [&](ulonglong2 *to, double chain) {
+            if (lane < 24) ll_store(to, ll_pack(chain, my_tag));
+        };
+        auto wait_word = [&](ulonglong2 w, const ulonglong2 *from) -> double {
+            if (!__all_sync(FULL, ll_ok(w, want_tag))) w = tri_poll(a, from, want_tag, dead, 40, t_chain);
             return ll_unpack(w);
         };
 
@@ -247,66 +241,94 @@ nbody_tri_kernel(const __grid_constant__ TriArgs a) {
             constexpr bool ALLV = decltype(allv)::value;
             const int nchunks = (j_end - j_begin) >> 5, M = 4 * nchunks;
             if (nchunks <= 0) return;
-            // chain word of minitile m of this item for this column lane
-            const size_t w0 = (size_t)(j_begin >> 5) * 96 + cc * 32 + cu;
-            auto word_at = [&](int m) { return w0 + (size_t)(m >> 2) * 96 + (m & 3) * 8; };
+            // Chain words of this item for this column lane: word of minitile m at wp0 + (m / 4) * 96 + (m % 4) * 8.
+            // The loop below walks them with one pointer and a step that alternates 16 / 80.
+            const ulonglong2 *wp = a.ll + (size_t)(j_begin >> 5) * 96 + cc * 32 + cu;   // word of minitile 0
+            const ptrdiff_t to_pub = pub - a.ll;
             // positions: chunk 0 straight into ring slot 0, chunk ch+1 into the other slot at the start of
             // chunk ch (from registers loaded one chunk earlier), so that the sources of the NEXT minitile can
             // always be fetched from shared memory before the current one is finished
-            ring[lane] = sx[j_begin + lane]; ring[32 + lane] = sy[j_begin + lane]; ring[64 + lane] = sz[j_begin + lane];
+            ring[lane] = sx[j_begin + lane]; ring[64 + lane] = sy[j_begin + lane]; ring[128 + lane] = sz[j_begin + lane];
             double fx = 0.0, fy = 0.0, fz = 0.0;                       // positions of chunk ch+1
             if (nchunks > 1) { const int g = j_begin + 32 + lane; fx = sx[g]; fy = sy[g]; fz = sz[g]; }
-            // chain words in flight: `wa` belongs to the minitile whose column pass comes next, `wb` to the one after
-            ulonglong2 wa = make_ulonglong2(0, 0), wb = ll_load(a.ll + word_at(0));
+            // chain words in flight, two minitiles ahead of their use: `we` of the even minitiles, `wo` of the
+            // odd ones (two registers that are never copied: a copy would wait for the load)
+            ulonglong2 we = ll_load(wp), wo = ll_load(wp + 8);
             __syncwarp();
             double xj[8], yj[8], zj[8];
-            auto fetch_sources = [&](const double *from) {
+            auto fetch_sources = [&](int m) {   // the 8 sources of minitile m: ring[x, y, z][slot (m / 4) % 2][32]
+                const double *from = ring + (m & 7) * 8;
 #pragma unroll
                 for (int u = 0; u < 8; u += 2) {
                     const double2 x2 = *reinterpret_cast<const double2 *>(from + u);
-                    const double2 y2 = *reinterpret_cast<const double2 *>(from + 32 + u);
-                    const double2 z2 = *reinterpret_cast<const double2 *>(from + 64 + u);
+                    const double2 y2 = *reinterpret_cast<const double2 *>(from + 64 + u);
+                    const double2 z2 = *reinterpret_cast<const double2 *>(from + 128 + u);
                     xj[u] = x2.x; xj[u + 1] = x2.y; yj[u] = y2.x; yj[u + 1] = y2.y; zj[u] = z2.x; zj[u + 1] = z2.y;
                 }
             };
-            fetch_sources(ring);
-            double chain = 0.0;
-#pragma unroll 1
-            for (int m = 0; m < M; ++m) {
-                const int q = m & 3, ch = m >> 2;
-                if (q == 0 && ch + 1 < nchunks) {   // the other ring slot was last read during chunk ch-1
-                    double *other = ring + ((ch + 1) & 1) * 96;
-                    other[lane] = fx; other[32 + lane] = fy; other[64 + lane] = fz;
+            auto next_chunk = [&](int ch) {   // start of chunk ch: chunk ch+1 into the other ring slot (last read during chunk ch-1)
+                if (ch + 1 < nchunks) {
+                    double *other = ring + ((ch + 1) & 1) * 32 + lane;
+                    other[0] = fx; other[64] = fy; other[128] = fz;
                     if (ch + 2 < nchunks) { const int g = j_begin + 32 * (ch + 2) + lane; fx = sx[g]; fy = sy[g]; fz = sz[g]; }
                 }
-                // minitile m: forces + row pass, fused with the column pass of minitile m-1
-                if (m > 0) chain = wait_word(wa, word_at(m - 1));
-                wa = wb;                                                // word of minitile m: consumed next iteration
-                if (m + 1 < M) wb = ll_load(a.ll + word_at(m + 1));     // two minitiles ahead of its use
-                double vx[8], vy[8], vz[8];
-                const double *col = tb + ((m + 1) & 1) * 24 * kTbPitch + col_lane * kTbPitch;   // buffer of minitile m-1
-                forces_and_column<ALLV>(px, py, pz, xj, yj, zj, vx, vy, vz, key, col, chain, cnt);
-                // the sources of the next minitile (their latency hides under the row pass)
-                if (m + 1 < M) fetch_sources(ring + (((m + 1) >> 2) & 1) * 96 + ((m + 1) & 3) * 8);
-                double *mine = tb + (m & 1) * 24 * kTbPitch + lane;
+            };
+            auto row_pass = [&](double *mine, const double (&vx)[8], const double (&vy)[8], const double (&vz)[8]) {
 #pragma unroll
-                for (int u = 0; u < 8; ++u) {   // row pass: sources ascending, the target's order
+                for (int u = 0; u < 8; ++u) {   // sources ascending, the target's order
                     ax = __dadd_rn(ax, vx[u]); ay = __dadd_rn(ay, vy[u]); az = __dadd_rn(az, vz[u]);
                     mine[u * kTbPitch] = vx[u]; mine[(8 + u) * kTbPitch] = vy[u]; mine[(16 + u) * kTbPitch] = vz[u];
                 }
-                if (m > 0) publish(word_at(m - 1), chain);
+            };
+            double *const tb0 = tb + lane, *const tb1 = tb + 24 * kTbPitch + lane;              // where this lane writes
+            const double *const col0 = tb + col_lane * kTbPitch, *const col1 = col0 + 24 * kTbPitch;   // ... and reads
+            // minitile m (parity known at compile time): forces + row pass, fused with the column pass of minitile
+            // m-1, whose word (at `at`) is in `w`; the register is refilled with the word of minitile m+1 (at
+            // `refill`, or null) and the sources of minitile m+1 are fetched under the row pass (FETCH)
+            auto minitile = [&](int m, ulonglong2 &w, const ulonglong2 *at, const ulonglong2 *refill,
+                                const double *col_prev, double *mine, auto fetch) {
+                double chain = wait_word(w, at);
+                if (refill) w = ll_load(refill);
+                double vx[8], vy[8], vz[8];
+                forces_and_column<ALLV>(px, py, pz, xj, yj, zj, vx, vy, vz, key, col_prev, chain, cnt);
+                if (decltype(fetch)::value) fetch_sources(m + 1);
+                row_pass(mine, vx, vy, vz);
+                publish(const_cast<ulonglong2 *>(at) + to_pub, chain);
                 __syncwarp();   // column lanes read these values during the next minitile; ring slot hand-over
+            };
+            {   // minitile 0: nothing before it to do a column pass for
+                fetch_sources(0);
+                next_chunk(0);
+                double qx[8], qy[8], qz[8], vx[8], vy[8], vz[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) { qx[u] = px; qy[u] = py; qz[u] = pz; }
+                pair_forces<8>(qx, qy, qz, xj, yj, zj, vx, vy, vz, key);
+                fetch_sources(1);
+                row_pass(tb0, vx, vy, vz);
+                __syncwarp();
             }
-            // column pass of the segment's last minitile (M-1 is odd: buffer 1; its word is in `wa`)
-            chain = wait_word(wa, word_at(M - 1));
-            const double *col = tb + 24 * kTbPitch + col_lane * kTbPitch;
+            int step = 16;   // words from minitile m-1 (even) to m+1: 16 inside a chunk, 80 across the chunk boundary
+#pragma unroll 1
+            for (int m = 1; m < M - 2; m += 2) {   // pairs (odd, even) = minitiles 1 .. M-2; wp = word of minitile m-1
+                check_range();
+                minitile(m, we, wp, wp + step, col0, tb1, std::true_type{});
+                if (step == 80) next_chunk((m + 1) >> 2);
+                minitile(m + 1, wo, wp + 8, wp + step + 8, col1, tb0, std::true_type{});
+                wp += step;
+                step = 96 - step;
+            }
+            check_range();
+            minitile(M - 1, we, wp, nullptr, col0, tb1, std::false_type{});
+            // column pass of the segment's last minitile (M-1 is odd: buffer 1, word in `wo`)
+            double chain = wait_word(wo, wp + 8);
 #pragma unroll
             for (int tcol = 0; tcol < 16; ++tcol) {
-                const double2 v = *reinterpret_cast<const double2 *>(col + 2 * tcol);
+                const double2 v = *reinterpret_cast<const double2 *>(col1 + 2 * tcol);
                 if (ALLV || 2 * tcol < cnt) chain = __dsub_rn(chain, v.x);
                 if (ALLV || 2 * tcol + 1 < cnt) chain = __dsub_rn(chain, v.y);
             }
-            publish(word_at(M - 1), chain);
+            check_range();
+            publish(const_cast<ulonglong2 *>(wp) + 8 + to_pub, chain);
             __syncwarp();
         };
         if (cnt == 32) lower(std::true_type{});
@@ -344,7 +366,8 @@ nbody_tri_kernel(const __grid_constant__ TriArgs a) {
                 double chain = seed[col_lane];
                 const double *col = tb + col_lane * kTbPitch;
                 for (int i = mt * 8 + cu + 1; i < cnt; ++i) chain = __dsub_rn(chain, col[i]);
-                publish((size_t)I * 96 + cc * 32 + mt * 8 + cu, chain);
+                check_range();
+                publish(pub + (size_t)I * 96 + cc * 32 + mt * 8 + cu, chain);
                 __syncwarp();
             }
             if (PROF) t_diag += now() - d0;
@@ -357,7 +380,7 @@ nbody_tri_kernel(const __grid_constant__ TriArgs a) {
         atomicAdd(c + 2, (unsigned long long)t_item); atomicAdd(c + 3, (unsigned long long)t_diag);
         atomicAdd(c + 4, (unsigned long long)n_items);
     }
-    if (!raised && __any_sync(FULL, key >= kRangeLimit)) tri_raise(a, 1);
+    if (__any_sync(FULL, key >= kRangeLimit)) tri_raise(a, 1);
 }
 
 // buffer[i] = G * acc[i] (reference src/nbody/nbody-run.c:22-24).  acc = what the LAST row published (tag

@@ -1,8 +1,8 @@
 #!/bin/bash
-# ncu --set full of the second-generation pair-symmetric kernel at N = 2^17 (a ~45 ms launch: the replay passes
-# of a spin-waiting kernel stay short), source page included.  The program is run once without ncu first.
+# ncu --set full of the second-generation pair-symmetric kernel at N = 2^19, source page included.
+# The program is run once without ncu first.
 mkdir -p gpurun_out
-timeout 120 python tools/prof_target.py sym 2002 131072 > gpurun_out/r2c_plain.log 2>&1; echo "plain_exit=$?"; cat gpurun_out/r2c_plain.log
-timeout 600 ncu --set full --import-source on --clock-control none -k regex:nbody_tri_kernel -c 1 -f -o gpurun_out/r2c_tri_2002 \
-    python tools/prof_target.py sym 2002 131072 > gpurun_out/r2c_ncu.log 2>&1; echo "ncu_exit=$?"; tail -5 gpurun_out/r2c_ncu.log
+timeout 120 python tools/prof_target.py sym 2002 524288 > gpurun_out/r2c_plain.log 2>&1; echo "plain_exit=$?"; cat gpurun_out/r2c_plain.log
+timeout 800 ncu --set full --import-source on --clock-control none -k regex:nbody_tri_kernel -c 1 -f -o gpurun_out/r2c_tri_2002_512k \
+    python tools/prof_target.py sym 2002 524288 > gpurun_out/r2c_ncu.log 2>&1; echo "ncu_exit=$?"; tail -5 gpurun_out/r2c_ncu.log
 ls -la gpurun_out/*.ncu-rep
