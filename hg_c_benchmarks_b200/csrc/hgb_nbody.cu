@@ -43,13 +43,19 @@ struct hgb_nbody {
     int cur = 0;  // state[cur] holds the newest positions
     bool uploaded = false;
     bool dynamics = false;  // hgb_nbody_set_dynamics was called
-    int sym = 0;            // pair-symmetric kernel variant R*100 + U*10 + CTAs/SM (0 = off)
-    int sym_min_n = 0;      // ... used when n >= sym_min_n, one GPU, EXACT mode
+    int sym = 0;            // pair-symmetric kernel variant R*100 + U*10 + CTAs/SM, or 2000 + CTAs/SM (0 = off)
+    bool sym_auto = false;  // the library picks the variant per GPU count (sym_variant_in_effect)
+    int sym_min_n = 0;      // ... used when n >= sym_min_n, EXACT mode
     int tri_seg = 0;        // second-generation kernel (variants 2000+): sources per segment,
     int tri_rows = 0;       // ... rows per tile,
     int tri_weight = 0;     // ... weight of the segment index in the ticket order (0 = defaults)
     unsigned tri_step = 0;  // steps run with it so far (epoch and buffer parity)
     int tri_status = 0;     // abort flag read back after the last advance
+    // chain-word buffers and control words of every shard as THIS process addresses them (own allocations,
+    // peer allocations of the same process, or cudaIpcOpenMemHandle mappings of the other ranks')
+    ulonglong2 *tri_peer_ll[2][kMaxPeers] = {};
+    int *tri_peer_ctl[kMaxPeers] = {};
+    int tri_connected = 0;  // 0 not tried, 1 tables filled, -1 the other ranks' buffers cannot be mapped (standard kernel is used)
     double dt = 0.0;
     std::vector<NbShard> sh;
 };
@@ -111,7 +117,8 @@ static int launch_step(const hgb_nbody *h, const NbShard &s, const double *src, 
 }
 
 // ---- pair-symmetric step (nbody_sym.cuh): one GPU, EXACT mode, all n targets --------------
-static int g_default_sym = -1, g_default_sym_min_n = -1;   // -1: read HGB_NBODY_SYM / HGB_NBODY_SYM_MIN_N
+static int g_default_sym = -1, g_default_sym_min_n = -1;
+static bool g_default_sym_auto = false;                    // HGB_NBODY_SYM unset or 1: the variant follows the GPU count   // -1: read HGB_NBODY_SYM / HGB_NBODY_SYM_MIN_N
 constexpr int kSymDefaultVariant = 242;                    // R = 2, U = 4, 2 CTAs (8 warps) per SM: profiles/r1e_nbody_sym_sweep_*.txt
 constexpr int kSymDefaultMinN = 393216;                    // measured: slower than the standard kernel at 2^18, 26 % faster at 2^19
 
@@ -141,17 +148,37 @@ static int launch_sym_variant(cudaStream_t st, int sms, const double *src, int n
 constexpr int kSymMaxN = 1 << 26;
 static_assert((kSymMaxN / 32) < (1 << 21) + 1, "worker id must fit the 21-bit tag field");
 
-static bool sym_applies(const hgb_nbody *h) {
-    if (h->sym == 0 || h->mode != HGB_NBODY_EXACT || h->n < h->sym_min_n || h->n >= kSymMaxN) return false;
-    if (tri_variant(h->sym))   // deals rows over GPUs: single-process handles with peer access
-        return h->world == 1 || (!h->rank_mode && h->exchange == HGB_EXCHANGE_P2P);
-    return h->world == 1;
+// Multi-GPU default: the second-generation kernel, when every GPU has at least this many bodies' worth of
+// rows to overlap the wavefront's ramp with (measured at N = 2^20: +32 % / +29 % / +11 % over the standard
+// kernel with ncclAllGather on 2 / 4 / 8 GPUs, profiles/r2j_tri_multi_rows_weight_g8_g4.txt; the ramp grows
+// with N and the work per GPU with N^2 / g, so smaller sets on many GPUs stay with the standard kernel)
+constexpr int kTriDefaultVariant = 2002;
+constexpr int kTriMinNPerGpu = 131072;
+
+// the pair-symmetric variant the next step of this handle runs (0 = the standard kernel)
+static int sym_variant_in_effect(const hgb_nbody *h) {
+    if (h->sym == 0 || h->mode != HGB_NBODY_EXACT || h->n >= kSymMaxN) return 0;
+    int v = h->sym, min_n = h->sym_min_n;
+    if (h->sym_auto && h->world > 1) {
+        v = kTriDefaultVariant;
+        min_n = std::max(min_n, kTriMinNPerGpu * h->world);
+    }
+    if (h->n < min_n) return 0;
+    if (!tri_variant(v)) return h->world == 1 ? v : 0;   // first generation: one GPU
+    if (h->world == 1) return v;
+    // rows dealt over GPUs: peer-mapped buffers -- of this process (peer-store handles) or of the other ranks (CUDA IPC)
+    if (!h->rank_mode) return h->exchange == HGB_EXCHANGE_P2P ? v : 0;
+    return h->tri_connected >= 0 ? v : 0;
 }
+static bool sym_applies(const hgb_nbody *h) { return sym_variant_in_effect(h) != 0; }
 
 // ---- second-generation pair-symmetric step (nbody_tri.cuh) ------------------------------------------
-constexpr int kTriDefaultSeg = 8192;      // sources per item
-constexpr int kTriDefaultRows = 16;       // rows per tile: rows of a tile start together and then stagger themselves
-constexpr int kTriDefaultWeight = 16;     // ticket order key = tile-row + weight * segment
+constexpr int kTriDefaultSeg = 16384;     // sources per item
+// rows per tile (rows of a tile start together and then stagger themselves; a tile-row is the unit dealt over
+// GPUs) and weight of the segment index in the ticket order (key = tile-row + weight * segment): one GPU /
+// several (profiles/r2e_tri_sweep.txt, r2j_tri_multi_rows_weight_g8_g4.txt)
+static int tri_default_rows(const hgb_nbody *h) { return h->world > 1 ? 16 : 8; }
+static int tri_default_weight(const hgb_nbody *h) { return h->world > 1 ? 64 : 32; }
 constexpr long long kTriSpinLimit = 10000000000ll;   // ~5 s of SM clock: a poll that long means a lost hand-off
 
 // Tiles (b, k): the `tr` rows of tile-row b against segment k, for every segment some row of b reaches.
@@ -162,8 +189,8 @@ constexpr long long kTriSpinLimit = 10000000000ll;   // ~5 s of SM clock: a poll
 // (I, k-1) is finished when (I, k) is handed out.  Tile-row b lives on shard b mod world.
 static int tri_plan(hgb_nbody *h, NbShard &s) {
     const int seg = h->tri_seg > 0 ? h->tri_seg : kTriDefaultSeg;
-    const int tr = h->tri_rows > 0 ? h->tri_rows : kTriDefaultRows;
-    const int weight = h->tri_weight > 0 ? h->tri_weight : kTriDefaultWeight;
+    const int tr = h->tri_rows > 0 ? h->tri_rows : tri_default_rows(h);
+    const int weight = h->tri_weight > 0 ? h->tri_weight : tri_default_weight(h);
     if (s.tri_tiles && s.tri_plan_seg == seg && s.tri_plan_rows == tr && s.tri_plan_weight == weight) return HGB_OK;
     const int T = (h->n + 31) / 32, TB = (T + tr - 1) / tr;
     std::vector<std::pair<long long, int2>> keyed;
@@ -206,6 +233,99 @@ static int tri_alloc(hgb_nbody *h) {
     return HGB_OK;
 }
 
+// what one rank tells the others about its buffers (CUDA IPC handles are plain 64-byte tokens)
+struct TriExport {
+    cudaIpcMemHandle_t ll[2], ctl;
+    int ok;
+    int pad[15];
+};
+
+// Fill the peer tables.  One process per GPU: every rank exports its two chain-word buffers and its control
+// words (cudaIpcGetMemHandle), the handles travel by ncclAllGather on the rank communicator, and every rank
+// maps the others' (cudaIpcOpenMemHandle, peer access enabled lazily).  COLLECTIVE over the ranks.  When any
+// rank cannot export or map (a container without shared IPC namespace, no peer access) all ranks agree to
+// keep the standard kernel: tri_connected = -1, not an error.
+static int tri_connect(hgb_nbody *h) {
+    if (h->tri_connected) return HGB_OK;
+    HGB_TRY(tri_alloc(h));
+    if (!h->rank_mode || h->world == 1) {
+        for (NbShard &s : h->sh) {
+            h->tri_peer_ll[0][s.index] = s.tri_ll[0]; h->tri_peer_ll[1][s.index] = s.tri_ll[1];
+            h->tri_peer_ctl[s.index] = s.tri_ctl;
+        }
+        h->tri_connected = 1;
+        return HGB_OK;
+    }
+    Runtime &r = rt();
+    NbShard &s = h->sh[0];
+    cudaStream_t st = s.dev->stream;
+    HGB_CUDA(cudaSetDevice(s.dev->device));
+    std::vector<TriExport> all(h->world);
+    TriExport mine;
+    memset(&mine, 0, sizeof mine);
+    mine.ok = cudaIpcGetMemHandle(&mine.ll[0], s.tri_ll[0]) == cudaSuccess &&
+              cudaIpcGetMemHandle(&mine.ll[1], s.tri_ll[1]) == cudaSuccess &&
+              cudaIpcGetMemHandle(&mine.ctl, s.tri_ctl) == cudaSuccess;
+    (void)cudaGetLastError();
+    TriExport *d = nullptr;
+    HGB_CUDA(cudaMalloc(&d, sizeof(TriExport) * h->world));
+    HGB_CUDA(cudaMemcpyAsync(d + r.rank, &mine, sizeof mine, cudaMemcpyHostToDevice, st));
+    HGB_NCCL(nccl().AllGather(d + r.rank, d, sizeof(TriExport), ncclChar, r.rank_comm, st));
+    HGB_CUDA(cudaMemcpyAsync(all.data(), d, sizeof(TriExport) * h->world, cudaMemcpyDeviceToHost, st));
+    HGB_CUDA(cudaStreamSynchronize(st));
+    bool ok = true;
+    for (const TriExport &e : all) ok = ok && e.ok;
+    std::vector<void *> opened;
+    if (ok) {
+        for (int p = 0; p < h->world && ok; ++p) {
+            if (p == r.rank) {
+                h->tri_peer_ll[0][p] = s.tri_ll[0]; h->tri_peer_ll[1][p] = s.tri_ll[1]; h->tri_peer_ctl[p] = s.tri_ctl;
+                continue;
+            }
+            void *m[3] = {nullptr, nullptr, nullptr};
+            const cudaIpcMemHandle_t *hd[3] = {&all[p].ll[0], &all[p].ll[1], &all[p].ctl};
+            for (int i = 0; i < 3 && ok; ++i) {
+                ok = cudaIpcOpenMemHandle(&m[i], *hd[i], cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+                if (ok) opened.push_back(m[i]);
+            }
+            h->tri_peer_ll[0][p] = (ulonglong2 *)m[0]; h->tri_peer_ll[1][p] = (ulonglong2 *)m[1]; h->tri_peer_ctl[p] = (int *)m[2];
+        }
+        (void)cudaGetLastError();
+    }
+    // every rank must take the same path: sum of the failures over the ranks (also the barrier behind which
+    // every rank's buffers are known to be zeroed and mapped)
+    double fails = ok ? 0.0 : 1.0;
+    double *dsum = reinterpret_cast<double *>(d);
+    HGB_CUDA(cudaMemcpyAsync(dsum, &fails, sizeof fails, cudaMemcpyHostToDevice, st));
+    HGB_NCCL(nccl().AllReduce(dsum, dsum, 1, ncclDouble, ncclSum, r.rank_comm, st));
+    HGB_CUDA(cudaMemcpyAsync(&fails, dsum, sizeof fails, cudaMemcpyDeviceToHost, st));
+    HGB_CUDA(cudaStreamSynchronize(st));
+    HGB_CUDA(cudaFree(d));
+    if (fails != 0.0) {
+        for (void *m : opened) cudaIpcCloseMemHandle(m);
+        (void)cudaGetLastError();
+        memset(h->tri_peer_ll, 0, sizeof h->tri_peer_ll);
+        memset(h->tri_peer_ctl, 0, sizeof h->tri_peer_ctl);
+        h->tri_connected = -1;
+        return HGB_OK;
+    }
+    h->tri_connected = 1;
+    return HGB_OK;
+}
+
+// unmap the other ranks' buffers (before the owners free them: hgb_nbody_destroy puts a barrier in between)
+static void tri_disconnect(hgb_nbody *h) {
+    if (h->tri_connected == 1 && h->rank_mode && h->world > 1) {
+        for (int p = 0; p < h->world; ++p) {
+            if (p == rt().rank) continue;
+            for (int b = 0; b < 2; ++b) if (h->tri_peer_ll[b][p]) cudaIpcCloseMemHandle(h->tri_peer_ll[b][p]);
+            if (h->tri_peer_ctl[p]) cudaIpcCloseMemHandle(h->tri_peer_ctl[p]);
+        }
+        (void)cudaGetLastError();
+    }
+    h->tri_connected = 0;
+}
+
 // shards that share one physical device (HGB_VIRTUAL_GPUS) must fit their persistent grids side by side
 static int tri_shards_on_device(const hgb_nbody *h, const NbShard &s) {
     int c = 0;
@@ -228,32 +348,27 @@ static int launch_tri_variant(const TriArgs &a, int grid, cudaStream_t st) {
     return HGB_OK;
 }
 
-// one step on every shard: tickets reset, wavefront kernels (all launched before any finish kernel), G*acc of
-// all n bodies from the final words (read from the shard that ran the last row), conditional redo by the standard kernel.  Every
-// shard ends with the complete next state: no exchange follows.
-static int launch_tri_step(hgb_nbody *h, int cur, int nxt) {
-    HGB_TRY(tri_alloc(h));
+// One step on every shard of this process: tickets reset, wavefront kernels (all launched before any finish
+// kernel), G*acc of all n bodies from the final words (read from the shard that ran the last row),
+// conditional redo by the standard kernel.  Every shard ends with the complete next state: no exchange follows.
+//
+// Nothing a PEER writes is ever reset while that peer could still write it, so the shards (or ranks) need no
+// barrier between steps: chain words carry the step's epoch and live in the buffer of the step's parity; a
+// shard can only be a step ahead of another (it needs the final words, which need every row); the range flag
+// of step s lives in slot 4 + parity(s), and slot 4 + parity(s+1) is cleared at the START of step s -- after
+// step s-1 has finished everywhere (its last user) and before anybody can be in step s+1.
+static int launch_tri_step(hgb_nbody *h, int variant, int cur, int nxt) {
     const unsigned step = h->tri_step++;
     const int parity = step & 1;
     const unsigned epoch_tag = (step % 2047 + 1) << 21;
     const int seg = h->sh[0].tri_plan_seg, rows = h->sh[0].tri_plan_rows, T = (h->n + 31) / 32;
-    const int ctas = h->sym % 10;
-    const bool prof = (h->sym / 10) % 10 == 1;
+    const int ctas = variant % 10;
+    const bool prof = (variant / 10) % 10 == 1;
     for (NbShard &s : h->sh) {
         HGB_CUDA(cudaSetDevice(s.dev->device));
-        HGB_CUDA(cudaMemsetAsync(s.tri_ctl, 0, 2 * sizeof(int), s.dev->stream));                       // ticket, range flag
+        HGB_CUDA(cudaMemsetAsync(s.tri_ctl, 0, sizeof(int), s.dev->stream));                           // ticket
+        HGB_CUDA(cudaMemsetAsync(s.tri_ctl + 4 + (parity ^ 1), 0, sizeof(int), s.dev->stream));        // next step's range flag
         HGB_CUDA(cudaMemsetAsync(s.tri_ctl + 8, 0, (kTriCtlInts - 8) * sizeof(int), s.dev->stream));   // profiling counters
-    }
-    if (h->world > 1) {
-        // a peer may raise flags in / publish into this shard's buffers as soon as ITS kernel runs: every
-        // shard's reset must be complete before any wavefront kernel starts
-        for (NbShard &s : h->sh) {
-            HGB_CUDA(cudaSetDevice(s.dev->device));
-            HGB_CUDA(cudaEventRecord(s.dev->ev_step, s.dev->stream));
-        }
-        for (NbShard &s : h->sh)
-            for (NbShard &o : h->sh)
-                if (&o != &s) HGB_CUDA(cudaStreamWaitEvent(s.dev->stream, o.dev->ev_step, 0));
     }
     for (NbShard &s : h->sh) {
         HGB_CUDA(cudaSetDevice(s.dev->device));
@@ -262,9 +377,10 @@ static int launch_tri_step(hgb_nbody *h, int cur, int nxt) {
         a.src = s.state[cur]; a.npad = h->npad; a.n = h->n; a.T = T; a.seg = seg; a.tr = rows;
         a.tiles = s.tri_tiles; a.ntiles = s.tri_ntiles;
         a.ll = s.tri_ll[parity];
-        a.ll_down = h->sh[(s.index + 1) % h->world].tri_ll[parity];   // tile-row b+1 lives on the next shard
+        a.ll_down = h->tri_peer_ll[parity][(s.index + 1) % h->world];   // tile-row b+1 lives on the next shard
         a.npeers = h->world;
-        for (int p = 0; p < h->world; ++p) a.ctl_all[p] = h->sh[p].tri_ctl;
+        for (int p = 0; p < h->world; ++p) a.ctl_all[p] = h->tri_peer_ctl[p];
+        a.range_slot = 4 + parity;
         a.racc = s.tri_racc; a.epoch_tag = epoch_tag; a.ctl = s.tri_ctl; a.spin_limit = kTriSpinLimit;
         const int grid = std::max(1, s.dev->sms * ctas / tri_shards_on_device(h, s));
         int rc = HGB_ERR_ARG;
@@ -275,7 +391,7 @@ static int launch_tri_step(hgb_nbody *h, int cur, int nxt) {
             case 5: rc = launch_tri_variant<2, true>(a, grid, s.dev->stream); break;
             case 6: rc = launch_tri_variant<3, false>(a, grid, s.dev->stream); break;
             case 7: rc = launch_tri_variant<3, true>(a, grid, s.dev->stream); break;
-            default: set_error("no nbody_tri variant %d", h->sym);
+            default: set_error("no nbody_tri variant %d", variant);
         }
         HGB_TRY(rc);
     }
@@ -285,8 +401,8 @@ static int launch_tri_step(hgb_nbody *h, int cur, int nxt) {
         // kernel that shares the device (virtual shards)
         const int fgrid = std::min((h->n + 255) / 256, std::max(1, s.dev->sms / tri_shards_on_device(h, s)));
         // the finished sums are the words of the LAST row, in the buffer of the shard that ran it
-        const NbShard &owner = h->sh[((T - 1) / rows) % h->world];
-        nbody_tri_finish_kernel<<<fgrid, 256, 0, s.dev->stream>>>(owner.tri_ll[parity], h->npad, h->n,
+        const ulonglong2 *final_words = h->tri_peer_ll[parity][((T - 1) / rows) % h->world];
+        nbody_tri_finish_kernel<<<fgrid, 256, 0, s.dev->stream>>>(final_words, h->npad, h->n,
                                                                  epoch_tag | (unsigned)T, s.state[nxt], s.tri_ctl,
                                                                  kTriSpinLimit);
         HGB_LAUNCHED();
@@ -295,13 +411,13 @@ static int launch_tri_step(hgb_nbody *h, int cur, int nxt) {
         PeerOut out;
         out.count = 1;
         out.base[0] = s.state[nxt];
-        HGB_TRY(launch_step(h, s, s.state[cur], 0, h->n, nullptr, out, nullptr, s.tri_ctl + 1));
+        HGB_TRY(launch_step(h, s, s.state[cur], 0, h->n, nullptr, out, nullptr, s.tri_ctl + 4 + parity));
     }
     return HGB_OK;
 }
 
 // whole step on shard s: tickets/flags reset, wavefront kernel, G*acc, conditional redo
-static int launch_sym(const hgb_nbody *h, NbShard &s, const double *src, const PeerOut &out) {
+static int launch_sym(const hgb_nbody *h, int variant, NbShard &s, const double *src, const PeerOut &out) {
     cudaStream_t st = s.dev->stream;
     if (!s.sym_ctl) {
         HGB_CUDA(cudaMalloc(&s.sym_ctl, sizeof(int) * kSymCtlInts));
@@ -315,7 +431,7 @@ static int launch_sym(const hgb_nbody *h, NbShard &s, const double *src, const P
     int sms = 0;
     HGB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s.dev->device));
     int rc = HGB_ERR_ARG;
-    switch (h->sym) {
+    switch (variant) {
 #define HGB_SYM(R_, U_, C_) case R_ * 100 + U_ * 10 + C_: rc = launch_sym_variant<R_, U_, C_>(st, sms, src, h->npad, h->n, ll, epoch_tag, s.sym_ctl); break;
         HGB_SYM(1, 2, 4) HGB_SYM(1, 4, 6) HGB_SYM(1, 4, 8) HGB_SYM(2, 2, 4) HGB_SYM(2, 2, 6) HGB_SYM(2, 2, 8)
         HGB_SYM(2, 4, 3) HGB_SYM(4, 1, 3) HGB_SYM(4, 2, 3) HGB_SYM(4, 2, 2) HGB_SYM(2, 4, 2) HGB_SYM(1, 8, 3)
@@ -324,7 +440,7 @@ static int launch_sym(const hgb_nbody *h, NbShard &s, const double *src, const P
         // diagnostic instantiations (clock64 spans -> hgb_nbody_sym_counters): variant + 1000
         case 1226: rc = launch_sym_variant<2, 2, 6, true>(st, sms, src, h->npad, h->n, ll, epoch_tag, s.sym_ctl); break;
         case 1242: rc = launch_sym_variant<2, 4, 2, true>(st, sms, src, h->npad, h->n, ll, epoch_tag, s.sym_ctl); break;
-        default: set_error("no pair-symmetric nbody variant %d", h->sym);
+        default: set_error("no pair-symmetric nbody variant %d", variant);
     }
     HGB_TRY(rc);
     nbody_sym_finish_kernel<<<(h->n + 255) / 256, 256, 0, st>>>(ll, h->npad, h->n, out);
@@ -351,6 +467,7 @@ static void sym_defaults(hgb_nbody *h) {
     if (g_default_sym < 0) {
         const char *e = getenv("HGB_NBODY_SYM");   // unset: on (default variant); 0: off; else a variant
         int v = e ? atoi(e) : 1;
+        g_default_sym_auto = v == 1;
         if (v == 1) v = kSymDefaultVariant;
         if (v == 2) v = 2002;
         g_default_sym = sym_variant_known(v) ? v : 0;
@@ -361,6 +478,7 @@ static void sym_defaults(hgb_nbody *h) {
         if (g_default_sym_min_n < 0) g_default_sym_min_n = 0;
     }
     h->sym = g_default_sym;
+    h->sym_auto = g_default_sym_auto;
     h->sym_min_n = g_default_sym_min_n;
 }
 
@@ -368,16 +486,18 @@ extern "C" {
 
 int hgb_nbody_set_symmetric(hgb_nbody *h, int variant, int min_n) {
     HGB_ARG(h, "handle");
+    const bool automatic = variant == 1;
     if (variant == 1) variant = kSymDefaultVariant;
     if (variant == 2) variant = 2002;
     HGB_ARG(variant == 0 || sym_variant_known(variant), "pair-symmetric variant (R*100 + U*10 + CTAs per SM, or 2000 + CTAs per SM)");
     HGB_ARG(min_n >= 0, "min_n");
     h->sym = variant;
+    h->sym_auto = automatic;
     h->sym_min_n = min_n;
     return HGB_OK;
 }
 
-int hgb_nbody_symmetric(const hgb_nbody *h) { return h && sym_applies(h) ? h->sym : 0; }
+int hgb_nbody_symmetric(const hgb_nbody *h) { return h ? sym_variant_in_effect(h) : 0; }
 
 int hgb_nbody_set_segment(hgb_nbody *h, int seg, int rows_per_tile, int order_weight) {
     HGB_ARG(h, "handle");
@@ -393,11 +513,12 @@ int hgb_nbody_describe(const hgb_nbody *h, char *buf, int capacity) {
     HGB_ARG(h && buf && capacity > 0, "handle / buffer");
     char kern[160];
     const bool fast = h->mode == HGB_NBODY_FAST;
-    if (sym_applies(h) && tri_variant(h->sym)) {
-        snprintf(kern, sizeof kern, "nbody_tri_kernel<%d> seg=%d rows=%d", h->sym % 10, h->tri_seg > 0 ? h->tri_seg : kTriDefaultSeg,
-                 h->tri_rows > 0 ? h->tri_rows : kTriDefaultRows);
-    } else if (sym_applies(h)) {
-        snprintf(kern, sizeof kern, "nbody_sym_kernel<%d,%d,%d>", h->sym / 100, h->sym / 10 % 10, h->sym % 10);
+    const int v = sym_variant_in_effect(h);
+    if (tri_variant(v)) {
+        snprintf(kern, sizeof kern, "nbody_tri_kernel<%d> seg=%d rows=%d weight=%d", v % 10, h->tri_seg > 0 ? h->tri_seg : kTriDefaultSeg,
+                 h->tri_rows > 0 ? h->tri_rows : tri_default_rows(h), h->tri_weight > 0 ? h->tri_weight : tri_default_weight(h));
+    } else if (v) {
+        snprintf(kern, sizeof kern, "nbody_sym_kernel<%d,%d,%d>", v / 100, v / 10 % 10, v % 10);
     } else {
         int block = 0, unroll = 0, warps = 0;
         const int count = h->n < h->slice ? h->n : h->slice;
@@ -408,7 +529,8 @@ int hgb_nbody_describe(const hgb_nbody *h, char *buf, int capacity) {
         snprintf(kern, sizeof kern, "nbody_step_kernel<%d,%d,%d,%s>", block, unroll, warps, fast ? "true" : "false");
     }
     const char *xchg = h->world == 1 ? "one GPU, no exchange"
-                     : (sym_applies(h) && tri_variant(h->sym)) ? "pair-symmetric: super-rows of targets dealt round-robin, chain words stored into the next GPU's buffer over NVLink, the last row broadcasts the finished sums (no position exchange)"
+                     : tri_variant(v) ? (h->rank_mode ? "pair-symmetric: tile-rows of targets dealt round-robin over the ranks, chain words stored into the next rank's buffer over NVLink (CUDA IPC mapping), finished sums read from the last row's rank, no position exchange"
+                                                      : "pair-symmetric: tile-rows of targets dealt round-robin, chain words stored into the next GPU's buffer over NVLink, finished sums read from the last row's GPU, no position exchange")
                      : h->exchange == HGB_EXCHANGE_P2P ? "targets sharded, results stored into every peer's next state over NVLink (fused epilogue)"
                                                        : "targets sharded, ncclAllGather of positions per step";
     snprintf(buf, (size_t)capacity, "%s | %s", kern, xchg);
@@ -418,14 +540,14 @@ int hgb_nbody_describe(const hgb_nbody *h, char *buf, int capacity) {
 double hgb_nbody_fp64_instr(const hgb_nbody *h) {
     if (!h) return 0.0;
     if (h->mode == HGB_NBODY_FAST) return 16.0;    // FMA-contracted rsqrt-Newton sequence
-    if (sym_applies(h) && tri_variant(h->sym)) return 16.5;   // 264 per 32 x 8 minitile: 26 + 3 per pair + 32 column instructions
+    if (tri_variant(sym_variant_in_effect(h))) return 16.5;   // 264 per 32 x 8 minitile: 26 + 3 per pair + 32 column instructions
     return sym_applies(h) ? 16.0 : 29.0;           // 32 per PAIR (26 + 3 + 3) vs 17 + 8 + 4 per interaction
 }
 
 int hgb_nbody_sym_counters(hgb_nbody *h, unsigned long long *out7) {
     HGB_ARG(h && out7, "handle / out");
     NbShard &s = h->sh[0];
-    int *ctl = tri_variant(h->sym) ? s.tri_ctl : s.sym_ctl;
+    int *ctl = tri_variant(sym_variant_in_effect(h)) ? s.tri_ctl : s.sym_ctl;
     if (!ctl) { set_error("the pair-symmetric kernel has not run on this handle"); return HGB_ERR_STATE; }
     HGB_CUDA(cudaSetDevice(s.dev->device));
     HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
@@ -447,6 +569,13 @@ int hgb_set_exchange(int kind) {
 
 int hgb_nbody_destroy(hgb_nbody *h) {
     if (!h) return HGB_OK;
+    if (h->tri_connected == 1 && h->rank_mode && h->world > 1) {
+        // the other ranks have this rank's buffers mapped: unmap theirs, then wait until everybody has
+        // (COLLECTIVE over the ranks, like the steps that used the mapping)
+        for (NbShard &s : h->sh) { cudaSetDevice(s.dev->device); cudaStreamSynchronize(s.dev->stream); }
+        tri_disconnect(h);
+        if (rt().rank_comm) hgb_comm_barrier();
+    }
     for (NbShard &s : h->sh) {
         cudaSetDevice(s.dev->device);
         cudaStreamSynchronize(s.dev->stream);
@@ -585,11 +714,16 @@ static int nb_advance(hgb_nbody *h, int iterations, float *ms, bool dyn) {
         HGB_CUDA(cudaSetDevice(s.dev->device));
         HGB_CUDA(cudaEventRecord(s.dev->ev_begin, s.dev->stream));
     }
-    const bool tri = !dyn && sym_applies(h) && tri_variant(h->sym);
+    if (!dyn && tri_variant(sym_variant_in_effect(h))) {
+        HGB_TRY(tri_connect(h));   // first use: buffers, peer tables (collective over the ranks); may turn the variant off
+        for (NbShard &s : h->sh) HGB_TRY(tri_plan(h, s));
+    }
+    const int variant = dyn ? 0 : sym_variant_in_effect(h);
+    const bool tri = tri_variant(variant);
     for (int it = 0; it < iterations; ++it) {
         const int cur = h->cur, nxt = cur ^ 1;
         if (tri) {   // rows dealt over the shards, every shard ends with the whole next state
-            HGB_TRY(launch_tri_step(h, cur, nxt));
+            HGB_TRY(launch_tri_step(h, variant, cur, nxt));
             h->cur = nxt;
             continue;
         }
@@ -611,8 +745,8 @@ static int nb_advance(hgb_nbody *h, int iterations, float *ms, bool dyn) {
                         s.state[cur], h->npad, h->n, t0, count, nullptr, out, nullptr, d);
                     HGB_LAUNCHED();
                 }
-            } else if (sym_applies(h)) {   // first-generation wavefront (variants R*100 + U*10 + CTAs)
-                HGB_TRY(launch_sym(h, s, s.state[cur], out));
+            } else if (variant) {   // first-generation wavefront (variants R*100 + U*10 + CTAs)
+                HGB_TRY(launch_sym(h, variant, s, s.state[cur], out));
             } else {
                 HGB_TRY(launch_step(h, s, s.state[cur], t0, count, nullptr, out, nullptr));
             }

@@ -42,7 +42,7 @@
 namespace hgb {
 
 constexpr int kTriWarps = 4;          // warps (independent workers) per CTA
-constexpr int kTriCtlInts = 32;       // ctl[0] ticket, ctl[1] range flag, ctl[2] abort flag, ctl[8..] profiling
+constexpr int kTriCtlInts = 32;       // ctl[0] ticket, ctl[2] abort flag, ctl[4], ctl[5] range flag of even / odd steps, ctl[8..] profiling
 constexpr int kTbPitch = 34;          // doubles per row of the transposed buffer (16-byte rows, conflict-free LDS.128)
 constexpr int kTriWarpDoubles = 2 * 3 * 32 + 2 * 24 * kTbPitch + 32;   // ring + 2 transposed buffers + chain seeds
 constexpr size_t kTriSmem = (size_t)kTriWarps * kTriWarpDoubles * sizeof(double);
@@ -62,6 +62,7 @@ struct TriArgs {
     int *ctl;
     int *ctl_all[kMaxPeers];  // peers' ctl (range / abort flags are raised everywhere)
     long long spin_limit;     // clock64 ticks a poll may last before the step is abandoned
+    int range_slot;           // ctl index of this step's range flag (4 + step parity)
 };
 
 // d * f of pair_wise_accel for one target against 8 sources, fused with the COLUMN pass of the
@@ -227,7 +228,7 @@ nbody_tri_kernel(const __grid_constant__ TriArgs a) {
         // flag is raised on every GPU BEFORE the last words computed from it are published, so whoever has
         // seen all final words of the step also sees the flag, and the ordinary kernel redoes the step.
         auto check_range = [&]() {
-            if (__any_sync(FULL, key >= kRangeLimit)) { tri_raise(a, 1); key = 0; }
+            if (__any_sync(FULL, key >= kRangeLimit)) { tri_raise(a, a.range_slot); key = 0; }
         };
         auto publish = [&](ulonglong2 *to, double chain) {
             if (lane < 24) ll_store(to, ll_pack(chain, my_tag));
@@ -380,7 +381,7 @@ nbody_tri_kernel(const __grid_constant__ TriArgs a) {
         atomicAdd(c + 2, (unsigned long long)t_item); atomicAdd(c + 3, (unsigned long long)t_diag);
         atomicAdd(c + 4, (unsigned long long)n_items);
     }
-    if (__any_sync(FULL, key >= kRangeLimit)) tri_raise(a, 1);
+    if (__any_sync(FULL, key >= kRangeLimit)) tri_raise(a, a.range_slot);
 }
 
 // buffer[i] = G * acc[i] (reference src/nbody/nbody-run.c:22-24).  acc = what the LAST row published (tag

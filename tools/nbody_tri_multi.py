@@ -18,7 +18,7 @@ pos = synth.uniform_cube(n, seed=1)
 
 
 def run(g, variant, seg=0, rows=0, weight=0, steps=2):
-    with H.nbody.NBody(n, ngpus=g) as nb:
+    with H.nbody.NBody(n, ngpus=g, exchange=H._abi.EXCHANGE_P2P if variant else H._abi.EXCHANGE_NCCL) as nb:
         nb.symmetric(variant, 0)
         if variant >= 2000:
             nb.segment(seg, rows, weight)
@@ -38,16 +38,23 @@ def run(g, variant, seg=0, rows=0, weight=0, steps=2):
 
 ref = None
 for g in gs:
+    if g == 1 and len(gs) > 1:
+        ms, out, _, what = run(1, 0)
+        ref = out
+        print(f"g=1 n={n} standard: {ms:9.3f} ms", flush=True)
+        continue
     ms, out, _, what = run(g, 0)
     if ref is None:
         ref = out
     print(f"g={g} n={n} standard: {ms:9.3f} ms  {n * n / (ms * 1e-3):.4e} inter/s  same={np.array_equal(out, ref)}  [{what}]", flush=True)
-    for variant, seg, rows, weight in ((2002, 16384, 8, 32), (2002, 16384, 4, 32), (2002, 8192, 8, 16), (2002, 32768, 8, 32),
-                                       (2002, 16384, 16, 32), (2002, 16384, 8, 8), (2003, 16384, 8, 32)):
+    grid = [(2002, 16384, r, w) for r in (16, 32, 64) for w in (32, 64, 128, 256)] + [(2002, 8192, r, w) for r in (16, 32) for w in (64, 128)]
+    if os.environ.get("TRI_GRID") == "small":
+        grid = [(2002, 16384, 8, 32), (2002, 16384, 16, 32), (2002, 16384, 16, 64), (2002, 8192, 16, 32), (2003, 16384, 16, 32)]
+    for variant, seg, rows, weight in grid:
         ms, out, _, what = run(g, variant, seg, rows, weight)
         print(f"g={g} n={n} tri {variant} seg={seg:6d} rows={rows:3d} weight={weight:3d}: {ms:9.3f} ms  "
-              f"{n * n / (ms * 1e-3):.4e} inter/s  same={np.array_equal(out, ref)}  [{what}]", flush=True)
-    ms, out, c, _ = run(g, 2012, 16384, 8, 32, steps=1)
+              f"{n * n / (ms * 1e-3):.4e} inter/s  same={np.array_equal(out, ref)}  [{what[0]}]", flush=True)
+    ms, out, c, _ = run(g, 2012, 16384, 16, 64, steps=1)
     tot = max(1, c[2])
     print(f"g={g} n={n} tri 2012 (profiling, shard 0): {ms:9.3f} ms; chain-word waits {100.0 * c[0] / tot:.1f} %, "
           f"row-accumulator waits {100.0 * c[1] / tot:.1f} %, items {c[4]}, cycles per item {tot / max(1, c[4]):.0f}", flush=True)

@@ -47,6 +47,40 @@ def main():
         assert np.array_equal(cur[sample], port.nbody_accel_subset(prev, sample)), ("nbody sample", n, rank)
         checks += 1
 
+    # ---- nbody: pair-symmetric wavefront, tile-rows dealt over the ranks, chain words through CUDA IPC mappings ----
+    tri_kernels = set()
+    for n, iters, seg, rows, weight in ((5000, 3, 256, 2, 0), (2048, 5, 64, 1, 4), (70001, 2, 4096, 4, 0), (1 << 17, 3, 0, 0, 0),
+                                        (33, 2, 32, 1, 1), (1 << 15, 4, 1024, 8, 2)):
+        pos = synth.plummer(n, seed=n + 1)
+        with H.nbody.NBody(n, ngpus=None, mode=H.NBODY_EXACT) as nb:
+            nb.symmetric(2002, 0).segment(seg, rows, weight)
+            nb.upload(pos)
+            nb.step(iters)
+            cur, prev = nb.download(want_prev=True)
+            tri_kernels.add(nb.describe()[0].split("<")[0])
+        if n <= 5000:
+            a, b = pos.copy(), np.zeros_like(pos)
+            port.nbody_run(a, b, iters)
+            w_cur, w_prev = (a, b) if iters % 2 == 0 else (b, a)
+            assert np.array_equal(cur, w_cur) and np.array_equal(prev, w_prev), ("nbody tri run", n, rank)
+        sample = np.unique(np.concatenate([np.random.default_rng(n).choice(n, min(n, 200), replace=False),
+                                           np.array([0, 1, 31, 32, n // 2, n - 2, n - 1])])).astype(np.int32)
+        assert np.array_equal(cur[sample], port.nbody_accel_subset(prev, sample)), ("nbody tri sample", n, rank)
+        checks += 1
+    # the default policy on a set large enough for every rank count: whatever kernel it picks, same bits
+    n = 131072 * max(1, world)
+    if n <= (1 << 20):
+        pos = synth.uniform_cube(n, seed=5)
+        with H.nbody.NBody(n, ngpus=None, mode=H.NBODY_EXACT) as nb:
+            nb.upload(pos)
+            nb.step(2)
+            cur, prev = nb.download(want_prev=True)
+            tri_kernels.add("default:" + nb.describe()[0].split(" ")[0])
+        sample = np.random.default_rng(7).choice(n, 96, replace=False).astype(np.int32)
+        assert np.array_equal(cur[sample], port.nbody_accel_subset(prev, sample)), ("nbody default policy", n, rank)
+        checks += 1
+    print(f"rank {rank}/{world}: pair-symmetric cases ran {sorted(tri_kernels)}", flush=True)
+
     # ---- convolution: row bands + halo exchange ------------------------------------------------
     for w, h, k, it, depth in ((300, 70, 3, 4, 0), (513, 260, 5, 3, 1), (640, 33, 7, 3, 0), (64, 5, 7, 2, 0),
                                (300, 1100, 3, 21, 0), (513, 1300, 7, 9, 3), (260, 2049, 5, 10, 0),
