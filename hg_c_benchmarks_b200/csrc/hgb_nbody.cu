@@ -368,7 +368,24 @@ static int launch_tri_step(hgb_nbody *h, int variant, int cur, int nxt) {
         HGB_CUDA(cudaSetDevice(s.dev->device));
         HGB_CUDA(cudaMemsetAsync(s.tri_ctl, 0, sizeof(int), s.dev->stream));                           // ticket
         HGB_CUDA(cudaMemsetAsync(s.tri_ctl + 4 + (parity ^ 1), 0, sizeof(int), s.dev->stream));        // next step's range flag
-        HGB_CUDA(cudaMemsetAsync(s.tri_ctl + 8, 0, (kTriCtlInts - 8) * sizeof(int), s.dev->stream));   // profiling counters
+        HGB_CUDA(cudaMemsetAsync(s.tri_ctl + 8, 0, 12 * sizeof(int), s.dev->stream));                  // profiling counters
+    }
+    // Shards that SHARE a device (HGB_VIRTUAL_GPUS, tests on a one-GPU box) do join their streams between
+    // steps: a shard's finish / redo / memset kernels (little shared memory) are not scheduled onto SMs
+    // that already run another shard's next wavefront kernel (large dynamic shared-memory carve-out), which
+    // in turn waits for this shard's next wavefront kernel -- a deadlock of the block scheduler, not of the
+    // algorithm (measured: the lagging shard's kernel did not start within the 5 s spin limit).
+    static const bool step_sync_env = getenv("HGB_NBODY_TRI_STEP_SYNC") != nullptr;
+    bool shared_device = false;
+    for (const NbShard &s : h->sh) shared_device = shared_device || tri_shards_on_device(h, s) > 1;
+    if ((step_sync_env || shared_device) && h->sh.size() > 1) {
+        for (NbShard &s : h->sh) {
+            HGB_CUDA(cudaSetDevice(s.dev->device));
+            HGB_CUDA(cudaEventRecord(s.dev->ev_step, s.dev->stream));
+        }
+        for (NbShard &s : h->sh)
+            for (NbShard &o : h->sh)
+                if (&o != &s) HGB_CUDA(cudaStreamWaitEvent(s.dev->stream, o.dev->ev_step, 0));
     }
     for (NbShard &s : h->sh) {
         HGB_CUDA(cudaSetDevice(s.dev->device));
@@ -793,8 +810,22 @@ static int nb_advance(hgb_nbody *h, int iterations, float *ms, bool dyn) {
             HGB_CUDA(cudaSetDevice(s.dev->device));
             HGB_CUDA(cudaMemcpy(&flag, s.tri_ctl + 2, sizeof(int), cudaMemcpyDeviceToHost));
             if (flag) {
-                HGB_CUDA(cudaMemset(s.tri_ctl + 2, 0, sizeof(int)));
-                set_error("pair-symmetric wavefront abandoned: a hand-off between rows did not arrive within the spin limit");
+                // what every shard was waiting for when it gave up (tickets handed out; first abandoned poll)
+                char msg[900];
+                int at = snprintf(msg, sizeof msg, "pair-symmetric wavefront abandoned: a hand-off between rows did not arrive within the spin limit;");
+                for (NbShard &o : h->sh) {
+                    int c[kTriCtlInts];
+                    HGB_CUDA(cudaSetDevice(o.dev->device));
+                    HGB_CUDA(cudaMemcpy(c, o.tri_ctl, sizeof c, cudaMemcpyDeviceToHost));
+                    HGB_CUDA(cudaMemset(o.tri_ctl + 2, 0, 2 * sizeof(int)));
+                    if (at < (int)sizeof msg - 1)
+                        at += snprintf(msg + at, sizeof msg - at, " shard %d: %d tickets of %d items%s", o.index, c[0], o.tri_ntiles * o.tri_plan_rows,
+                                       c[3] ? "" : ", no poll abandoned here;");
+                    if (c[3] && at < (int)sizeof msg - 1)
+                        at += snprintf(msg + at, sizeof msg - at, ", wanted tag epoch %u id %d, found tag %#x, chain word %d, row-accumulator word %d;",
+                                       (unsigned)c[6] >> 21, c[6] & 0x1fffff, (unsigned)c[24], c[25], c[26]);
+                }
+                set_error("%s", msg);
                 return HGB_ERR_STATE;
             }
         }

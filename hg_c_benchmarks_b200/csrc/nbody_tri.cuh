@@ -21,7 +21,10 @@
 //     dependent instructions with 24 of 32 lanes busy: 264 instead of the ideal 256 per minitile)
 //     and publishes the result for the next row.  The column pass of minitile m is issued INSIDE the
 //     force evaluation of minitile m+1 (one basic block, independent instruction streams), so its
-//     latency hides under the throughput-bound part.
+//     latency hides under the throughput-bound part.  (Measured alternative: the chain packed into the
+//     first stages and published mid-block, chain words prefetched one minitile ahead instead of two --
+//     a shorter stagger between rows, but 8-12 % less throughput on one GPU and no gain on 4 / 8 GPUs,
+//     profiles/r2m_tri_multi_early_publish_g8_g4.txt.)
 //   * Hand-off between rows: tagged words (payload + tag in every 8-byte half: one 16-byte store
 //     publishes value and flag, no fence; the "LL" scheme of collective libraries).  Row I expects
 //     tag (epoch | I), written by row I-1, and publishes with (epoch | I+1) -- into the local buffer,
@@ -42,7 +45,7 @@
 namespace hgb {
 
 constexpr int kTriWarps = 4;          // warps (independent workers) per CTA
-constexpr int kTriCtlInts = 32;       // ctl[0] ticket, ctl[2] abort flag, ctl[4], ctl[5] range flag of even / odd steps, ctl[8..] profiling
+constexpr int kTriCtlInts = 32;       // ctl[0] ticket, ctl[2] abort flag, ctl[4], ctl[5] range flag of even / odd steps, ctl[8..19] profiling, ctl[3], [6], [7], [24..26] what an abandoned poll waited for
 constexpr int kTbPitch = 34;          // doubles per row of the transposed buffer (16-byte rows, conflict-free LDS.128)
 constexpr int kTriWarpDoubles = 2 * 3 * 32 + 2 * 24 * kTbPitch + 32;   // ring + 2 transposed buffers + chain seeds
 constexpr size_t kTriSmem = (size_t)kTriWarps * kTriWarpDoubles * sizeof(double);
@@ -163,7 +166,16 @@ __device__ __noinline__ ulonglong2 tri_poll(const TriArgs &a, const ulonglong2 *
         w = ll_load(q);
         if (__all_sync(0xffffffffu, ll_ok(w, tag))) break;
         bool g = *reinterpret_cast<volatile int *>(a.ctl + 2) != 0;
-        if (!g && clock64() - t0 > a.spin_limit) { tri_raise(a, 2); g = true; }
+        if (!g && clock64() - t0 > a.spin_limit) {
+            if ((threadIdx.x & 31) == 0 && atomicCAS(a.ctl + 3, 0, 1) == 0) {   // first to give up: say what never came
+                a.ctl[6] = (int)tag;
+                a.ctl[7] = (int)(unsigned)w.x; a.ctl[24] = (int)(w.x >> 32);
+                const long long off = q - a.ll, roff = q - a.racc;
+                a.ctl[25] = (off >= 0 && off < 3ll * a.npad) ? (int)off : -1;
+                a.ctl[26] = (roff >= 0 && roff < 3ll * a.npad) ? (int)roff : -1;
+            }
+            tri_raise(a, 2); g = true;
+        }
         dead = __any_sync(0xffffffffu, g);
         __nanosleep(ns);
     }

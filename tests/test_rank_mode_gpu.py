@@ -25,6 +25,9 @@ def _run(world):
            os.path.join(ROOT, "tools", "rank_mode_check.py")]
     r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=1500)
     assert r.returncode == 0, (r.stdout[-3000:], r.stderr[-3000:])
+    for line in r.stdout.splitlines():   # kept in the log (pytest -s): which kernels ran on every rank
+        if "RANK_MODE_OK" in line or "pair-symmetric cases" in line:
+            print(line)
     for rank in range(world):
         assert f"RANK_MODE_OK rank {rank}/{world}" in r.stdout, r.stdout[-3000:]
 
