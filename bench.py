@@ -113,6 +113,31 @@ def ncu_traffic(kernel_prefix):
     return None
 
 
+def pcie_probe(device):
+    """pinned-memory copy rates of this box, both directions AT ONCE (what a streamed run can reach at best):
+    ms per GiB for H2D and D2H, CUDA events on two torch streams"""
+    import torch
+    n = 1 << 27                                               # 1 GiB of doubles
+    a_h, b_h = torch.empty(n, dtype=torch.float64).pin_memory(), torch.empty(n, dtype=torch.float64).pin_memory()
+    a_d, b_d = torch.empty(n, dtype=torch.float64, device=device), torch.zeros(n, dtype=torch.float64, device=device)
+    s1, s2 = torch.cuda.Stream(device), torch.cuda.Stream(device)
+    res = {}
+    for rep in range(2):
+        torch.cuda.synchronize(device)
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        with torch.cuda.stream(s1):
+            e[0].record(); a_d.copy_(a_h, non_blocking=True); e[1].record()
+        with torch.cuda.stream(s2):
+            e[2].record(); b_h.copy_(b_d, non_blocking=True); e[3].record()
+        torch.cuda.synchronize(device)
+        res = {"h2d_ms_per_gib": e[0].elapsed_time(e[1]), "d2h_ms_per_gib": e[2].elapsed_time(e[3])}
+    res["h2d_GBps"] = 2 ** 30 / (res["h2d_ms_per_gib"] * 1e-3) / 1e9
+    res["d2h_GBps"] = 2 ** 30 / (res["d2h_ms_per_gib"] * 1e-3) / 1e9
+    res["what"] = "1 GiB pinned host <-> device, both directions concurrently"
+    del a_h, b_h, a_d, b_d
+    return res
+
+
 def pinned(shape):
     """numpy array backed by pinned host memory (the e2e legs copy from/to pinned buffers)"""
     import torch
@@ -525,6 +550,7 @@ def main():
                       ("5x5_fast", 5, unit(synth.kernel_dense(5)), "float", True),
                       ("7x7_fast", 7, unit(synth.kernel_dense(7)), "float", True),
                       ("3x3_int_image", 3, synth.kernel_dense(3), "int", False)]
+        pcie = pcie_probe(local_rank) if world == 1 else None
         dense, dense_kind = None, None
         for key, k, kern, kind, fast in cases:
             if kind != dense_kind:
@@ -547,14 +573,27 @@ def main():
             l0 = L.hgb_launch_count()
             ms = max_over_ranks(cv.step(CONV_TIMED))          # inputs (2 GiB) >> L2: no flush needed
             conv_launches = L.hgb_launch_count() - l0
-            barrier()
-            t0 = time.perf_counter()                          # e2e: H2D band, iterations, D2H band
-            cv.upload(band)
-            cv.step(CONV_ITERS)
-            cv.download(out=got)
-            barrier()
-            e2e = max_over_ranks((time.perf_counter() - t0) * 1e3)
-            cv.close()
+            streamed = world == 1 and not fast
+            if streamed:
+                # the drop-in call (hgb_conv_run, state n-1 not requested): row chunks streamed over PCIe under
+                # the iterations of other chunks.  In place, so the input is copied into `got` first (not timed);
+                # one untimed call before it (chunk handle, staging buffers)
+                cv.close()
+                for timed in (False, True):
+                    got[...] = band
+                    barrier()
+                    t0 = time.perf_counter()
+                    H.convolution.run_flat(got, None, cn, cn, p, kern, CONV_ITERS, 1)
+                    e2e = (time.perf_counter() - t0) * 1e3
+            else:
+                barrier()
+                t0 = time.perf_counter()                      # e2e: H2D band, iterations, D2H band
+                cv.upload(band)
+                cv.step(CONV_ITERS)
+                cv.download(out=got)
+                barrier()
+                e2e = max_over_ranks((time.perf_counter() - t0) * 1e3)
+                cv.close()
             okc, cntc, errc = conv_parity(got, dense, r0, rows, cn, p, kern, CONV_ITERS, tol=1e-12 if fast else 0.0)
             parity[f"conv_{key}"] = {"ok": all_ok(okc), "rows": total(cntc),
                                      "of": f"{CONV_ITERS} iterations (the e2e leg's result), 3 bands of <= {PARITY_BAND} rows per rank incl. band seams",
@@ -577,6 +616,10 @@ def main():
                      "ms_per_iteration": ms / CONV_TIMED, "iterations": CONV_TIMED, "gpu_launches": int(conv_launches),
                      "workload": f"{cn}x{cn} {image_desc}, {kern_desc}, row bands over {world} GPU(s)",
                      "e2e_GBps": cn * cn * BYTES_PER_PIXEL * CONV_ITERS / (e2e * 1e-3) / 1e9,
+                     "e2e_call": ("hgb_conv_run(cur, prev=NULL): row chunks streamed, H2D / iterations / D2H on three streams"
+                                  if streamed else "hgb_conv_upload + hgb_conv_step + hgb_conv_download of the rank's band, one after the other"),
+                     "e2e_pcie_bound_GBps": (cn * cn * BYTES_PER_PIXEL * CONV_ITERS / (max(pcie["h2d_ms_per_gib"], pcie["d2h_ms_per_gib"])
+                                             * (cn * (cn + 2 * p) * 8 / 2 ** 30) * 1e-3) / 1e9) if streamed else None,
                      "roofline": {"bound": "hbm", "achieved": gbps / world, "peak": peak,
                                   "unit": "GB/s", "frac": gbps / world / peak,
                                   "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if "hbm_gbs" in peaks else "fallback 6650 (of fallback)",
@@ -596,6 +639,8 @@ def main():
                                           "peak_source": "clock-true issue rate: SMs x 64 lanes x SM clock sampled during the nbody steps",
                                           "note": "exact mode needs a DMUL and a DADD per tap (no FMA)"}
             conv[key] = entry
+        if pcie:
+            conv["pcie_probe"] = pcie
         del dense
 
     if rank == 0:

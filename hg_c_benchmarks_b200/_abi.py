@@ -66,6 +66,8 @@ SIGNATURES = {
     "hgb_conv_run": (C.c_int, [_dp, _dp, C.c_int, C.c_int, C.c_int, _dp, C.c_int, C.c_int, C.c_int,
                                C.c_int]),
     "hgb_set_conv_mode": (C.c_int, [C.c_int]),
+    "hgb_set_conv_streaming": (C.c_int, [C.c_int]),
+    "hgb_conv_unpin": (C.c_int, []),
     "hgb_conv_set_mode": (C.c_int, [_vp, C.c_int]),
     "hgb_conv_mode_in_effect": (C.c_int, [_vp]),
     "hgb_conv_create": (C.c_int, [C.POINTER(_vp), C.c_int, C.c_int, C.c_int, C.c_int]),

@@ -174,6 +174,25 @@ def run_on_padded_image(padded_img, kernel, args, buffer):
     padded_img[0], buffer[0] = img, buf
 
 
+def run_flat(cur, prev, inner_w, inner_h, padding, kernel, iterations, ngpus=1):
+    """hgb_conv_run on flat host arrays: `cur` (inner_h rows of inner_w + 2*padding doubles) holds the
+    input and receives state n; `prev` receives state n-1, or None when it is not wanted.  One GPU and a
+    tall image: streamed in row chunks, PCIe copies under the iterations (set_streaming)."""
+    kern = np.ascontiguousarray(kernel, dtype=np.float64)
+    check(lib().hgb_conv_run(dptr(cur), dptr(prev) if prev is not None else None, int(inner_w), int(inner_h),
+                             int(padding), dptr(kern), kern.shape[1], kern.shape[0], int(iterations), int(ngpus)))
+
+
+def set_streaming(chunk_rows=1):
+    """0: hgb_conv_run never streams; 1: automatic chunking (default); else valid rows per chunk"""
+    check(lib().hgb_set_conv_streaming(int(chunk_rows)))
+
+
+def unpin():
+    """release the page-lock registrations hgb_conv_run keeps on caller buffers (before freeing them)"""
+    check(lib().hgb_conv_unpin())
+
+
 def apply_kernel_to_padded_image(padded_img, kernel, args, buffer):
     """one stencil pass into the INNER region of `buffer`, pad columns untouched
     (reference src/convolution/convolution-run.c:52-62)."""

@@ -1,6 +1,9 @@
 // hgb_conv.cu -- host side of the convolution path: device-resident bands,
 // row-band sharding with halo exchange (ncclSend/ncclRecv or peer copies) and the
 // drop-in for run_on_padded_image() (reference src/convolution/convolution-run.c:41-49).
+#include <algorithm>
+#include <vector>
+
 #include "hgb_common.cuh"
 #include "conv_kernels.cuh"
 
@@ -691,6 +694,223 @@ int hgb_set_conv_mode(int mode) {
     return HGB_OK;
 }
 
+// ---- streamed drop-in: the PCIe copies of row chunks run under the iterations of other chunks ----------
+// One GPU, EXACT mode, images much taller than a chunk.  The image is cut into chunks of `Hs` rows that
+// overlap by 2F, F = iterations * p: after `iterations` passes over a chunk taken as an image of its own
+// (its artificial top/bottom edges clamp like real ones, which is wrong), exactly the rows closer than F to
+// an artificial edge are wrong, so the chunks' valid rows tile the image and every valid pixel went through
+// the same arithmetic as in the one-piece run: bit-identical.  Three streams: H2D of chunk c+1 (only rows
+// not yet on the device; the overlap is copied device-to-device from the previous staging buffer), the
+// iterations of chunk c on the sub-handle's stream, D2H of chunk c-1.  In-place (cur is input and output)
+// is safe: a chunk's result rows end F rows above the first row the next H2D reads.
+namespace {
+struct CvPipe {
+    hgb_conv *sub = nullptr;
+    int W = 0, Hs = 0, p = 0;
+    size_t cap = 0;                                  // doubles per staging buffer
+    double *din[2] = {nullptr, nullptr}, *dout[2] = {nullptr, nullptr}, *dprev[2] = {nullptr, nullptr};
+    cudaStream_t s_in = nullptr, s_out = nullptr;
+    cudaEvent_t ev_in[2] = {}, ev_loaded[2] = {}, ev_res[2] = {}, ev_out[2] = {};
+    bool events = false;
+    void *reg[2] = {nullptr, nullptr};               // caller buffers page-locked by cudaHostRegister
+    size_t reg_bytes[2] = {0, 0};
+};
+CvPipe g_pipe;
+
+void pipe_unpin() {
+    for (int i = 0; i < 2; ++i) {
+        if (g_pipe.reg[i]) cudaHostUnregister(g_pipe.reg[i]);
+        g_pipe.reg[i] = nullptr; g_pipe.reg_bytes[i] = 0;
+    }
+    (void)cudaGetLastError();
+}
+
+void pipe_free() {
+    pipe_unpin();
+    hgb_conv_destroy(g_pipe.sub);
+    g_pipe.sub = nullptr;
+    for (int b = 0; b < 2; ++b) {
+        cudaFree(g_pipe.din[b]); cudaFree(g_pipe.dout[b]); cudaFree(g_pipe.dprev[b]);
+        g_pipe.din[b] = g_pipe.dout[b] = g_pipe.dprev[b] = nullptr;
+    }
+    if (g_pipe.events) {
+        for (int b = 0; b < 2; ++b) {
+            cudaEventDestroy(g_pipe.ev_in[b]); cudaEventDestroy(g_pipe.ev_loaded[b]);
+            cudaEventDestroy(g_pipe.ev_res[b]); cudaEventDestroy(g_pipe.ev_out[b]);
+        }
+        cudaStreamDestroy(g_pipe.s_in); cudaStreamDestroy(g_pipe.s_out);
+        g_pipe.events = false;
+    }
+    g_pipe.W = g_pipe.Hs = g_pipe.p = 0; g_pipe.cap = 0;
+}
+
+// async copies overlap only from page-locked memory: is [ptr, ptr+bytes) page-locked already (cudaHostAlloc,
+// torch pinned memory, an earlier registration)?  Otherwise register it and remember (slot 0: cur, 1: prev).
+int pipe_pin(int slot, void *ptr, size_t bytes) {
+    if (g_pipe.reg[slot] == ptr && g_pipe.reg_bytes[slot] >= bytes) return HGB_OK;
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, ptr) == cudaSuccess && at.type == cudaMemoryTypeHost) {
+        cudaPointerAttributes end;
+        if (cudaPointerGetAttributes(&end, (char *)ptr + bytes - 1) == cudaSuccess && end.type == cudaMemoryTypeHost) return HGB_OK;
+    }
+    (void)cudaGetLastError();
+    if (g_pipe.reg[slot]) { cudaHostUnregister(g_pipe.reg[slot]); g_pipe.reg[slot] = nullptr; g_pipe.reg_bytes[slot] = 0; }
+    (void)cudaGetLastError();
+    if (cudaHostRegister(ptr, bytes, cudaHostRegisterDefault) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return HGB_ERR_STATE;   // the caller falls back to the one-piece path
+    }
+    g_pipe.reg[slot] = ptr; g_pipe.reg_bytes[slot] = bytes;
+    return HGB_OK;
+}
+
+int pipe_setup(int W, int Hs, int p) {
+    if (g_pipe.sub && g_pipe.W == W && g_pipe.Hs == Hs && g_pipe.p == p) return HGB_OK;
+    void *keep[2] = {g_pipe.reg[0], g_pipe.reg[1]};
+    size_t keep_b[2] = {g_pipe.reg_bytes[0], g_pipe.reg_bytes[1]};
+    g_pipe.reg[0] = g_pipe.reg[1] = nullptr;          // registrations survive a change of geometry
+    pipe_free();
+    g_pipe.reg[0] = keep[0]; g_pipe.reg[1] = keep[1]; g_pipe.reg_bytes[0] = keep_b[0]; g_pipe.reg_bytes[1] = keep_b[1];
+    HGB_TRY(hgb_conv_create(&g_pipe.sub, W, Hs, p, 1));
+    g_pipe.W = W; g_pipe.Hs = Hs; g_pipe.p = p;
+    g_pipe.cap = (size_t)Hs * (W + 2 * p);
+    CvShard &s = g_pipe.sub->sh[0];
+    HGB_CUDA(cudaSetDevice(s.dev->device));
+    for (int b = 0; b < 2; ++b) {
+        HGB_CUDA(cudaMalloc(&g_pipe.din[b], g_pipe.cap * sizeof(double)));
+        HGB_CUDA(cudaMalloc(&g_pipe.dout[b], g_pipe.cap * sizeof(double)));
+    }
+    HGB_CUDA(cudaStreamCreateWithFlags(&g_pipe.s_in, cudaStreamNonBlocking));
+    HGB_CUDA(cudaStreamCreateWithFlags(&g_pipe.s_out, cudaStreamNonBlocking));
+    for (int b = 0; b < 2; ++b) {
+        HGB_CUDA(cudaEventCreateWithFlags(&g_pipe.ev_in[b], cudaEventDisableTiming));
+        HGB_CUDA(cudaEventCreateWithFlags(&g_pipe.ev_loaded[b], cudaEventDisableTiming));
+        HGB_CUDA(cudaEventCreateWithFlags(&g_pipe.ev_res[b], cudaEventDisableTiming));
+        HGB_CUDA(cudaEventCreateWithFlags(&g_pipe.ev_out[b], cudaEventDisableTiming));
+    }
+    g_pipe.events = true;
+    return HGB_OK;
+}
+
+static int g_stream_rows = -1;   // -1: HGB_CONV_STREAM_ROWS from the environment (0 = off); else rows per chunk
+}  // namespace
+
+int hgb_set_conv_streaming(int chunk_rows) {
+    HGB_ARG(chunk_rows >= 0, "chunk rows (0 = never stream, 1 = automatic)");
+    g_stream_rows = chunk_rows;
+    return HGB_OK;
+}
+
+int hgb_conv_unpin(void) {
+    pipe_unpin();
+    return HGB_OK;
+}
+
+// rows per chunk for this call, or 0: run in one piece
+static int stream_plan(int inner_w, int inner_h, int padding, int iterations, int g, const double *prev, int *Hs_out) {
+    (void)prev;
+    if (g_stream_rows < 0) {
+        const char *e = getenv("HGB_CONV_STREAM_ROWS");
+        g_stream_rows = e ? atoi(e) : 1;
+        if (g_stream_rows < 0) g_stream_rows = 0;
+    }
+    if (g_stream_rows == 0 || g != 1 || g_cv_mode == HGB_CONV_FAST) return 0;   // FAST classifies the WHOLE image first
+    const long F = (long)iterations * padding;
+    long valid = g_stream_rows;
+    if (valid == 1) {   // automatic: ~32 MiB of valid rows per chunk, never less than 8 F (fringe work <= 25 %)
+        valid = (32l << 20) / (8l * (inner_w + 2 * padding));
+        valid = std::max(valid, std::max(64l, 8 * F));
+    }
+    const long Hs = valid + 2 * F;
+    if (Hs > (1 << 20) || inner_h < 3 * Hs) return 0;       // fewer than ~3 chunks: nothing to overlap
+    *Hs_out = (int)Hs;
+    return 1;
+}
+
+static int conv_run_streamed(double *cur, double *prev, int W, int H, int p, const double *kernel, int kw, int kh,
+                             int iterations, int Hs) {
+    const size_t hp = (size_t)W + 2 * p;
+    const int F = iterations * p;
+    if (pipe_pin(0, cur, (size_t)H * hp * sizeof(double)) != HGB_OK) return HGB_ERR_STATE;
+    if (prev && pipe_pin(1, prev, (size_t)H * hp * sizeof(double)) != HGB_OK) return HGB_ERR_STATE;
+    HGB_TRY(pipe_setup(W, Hs, p));
+    CvPipe &P = g_pipe;
+    hgb_conv *sub = P.sub;
+    CvShard &s = sub->sh[0];
+    cudaStream_t sc = s.dev->stream;
+    HGB_CUDA(cudaSetDevice(s.dev->device));
+    if (prev)
+        for (int b = 0; b < 2; ++b)
+            if (!P.dprev[b]) HGB_CUDA(cudaMalloc(&P.dprev[b], P.cap * sizeof(double)));
+    sub->uploaded = false;
+    HGB_TRY(hgb_conv_set_mode(sub, HGB_CONV_EXACT));
+    HGB_TRY(hgb_conv_set_kernel(sub, kernel, kw, kh));
+    // chunk c: sub-image rows [s0, s0 + Hs), valid result rows [v0, v1)
+    struct Chunk { int s0, v0, v1; };
+    std::vector<Chunk> chunks;
+    for (int done = 0; done < H;) {
+        Chunk c;
+        c.s0 = std::min(done == 0 ? 0 : done - F, H - Hs);
+        c.v0 = done;
+        c.v1 = (c.s0 + Hs >= H) ? H : c.s0 + Hs - F;
+        chunks.push_back(c);
+        done = c.v1;
+    }
+    const int nc = (int)chunks.size();
+    auto enqueue_h2d = [&](int c) -> int {   // rows of chunk c into din[c & 1]
+        const int b = c & 1;
+        const Chunk &k = chunks[c];
+        if (c >= 2) HGB_CUDA(cudaStreamWaitEvent(P.s_in, P.ev_loaded[b], 0));   // chunk c-2 has left this buffer
+        int fresh0 = k.s0;
+        if (c > 0) {   // rows already on the device: the tail of the previous chunk's staging buffer
+            const Chunk &q = chunks[c - 1];
+            const int have1 = q.s0 + Hs;
+            if (have1 > k.s0) {
+                HGB_CUDA(cudaMemcpyAsync(P.din[b], P.din[b ^ 1] + (size_t)(k.s0 - q.s0) * hp,
+                                         (size_t)(have1 - k.s0) * hp * sizeof(double), cudaMemcpyDeviceToDevice, P.s_in));
+                fresh0 = have1;
+            }
+        }
+        if (fresh0 < k.s0 + Hs)
+            HGB_CUDA(cudaMemcpyAsync(P.din[b] + (size_t)(fresh0 - k.s0) * hp, cur + (size_t)fresh0 * hp,
+                                     (size_t)(k.s0 + Hs - fresh0) * hp * sizeof(double), cudaMemcpyHostToDevice, P.s_in));
+        HGB_CUDA(cudaEventRecord(P.ev_in[b], P.s_in));
+        return HGB_OK;
+    };
+    HGB_TRY(enqueue_h2d(0));
+    for (int c = 0; c < nc; ++c) {
+        const int b = c & 1;
+        const Chunk &k = chunks[c];
+        if (c + 1 < nc) HGB_TRY(enqueue_h2d(c + 1));
+        // the chunk becomes state 0 of the sub-handle (device-to-device, host pitch -> device pitch)
+        HGB_CUDA(cudaStreamWaitEvent(sc, P.ev_in[b], 0));
+        HGB_CUDA(cudaMemcpy2DAsync(s.img[0] + (size_t)sub->halo * sub->dp + kLead - p, sub->dp * sizeof(double), P.din[b],
+                                   hp * sizeof(double), hp * sizeof(double), Hs, cudaMemcpyDeviceToDevice, sc));
+        HGB_CUDA(cudaEventRecord(P.ev_loaded[b], sc));
+        sub->cur = 0; sub->uploaded = true; sub->valid_xr = sub->halo; sub->integer_input = false;
+        HGB_TRY(hgb_conv_step(sub, iterations, nullptr));
+        // valid rows -> staging (device pitch -> host pitch), then home on the D2H stream
+        if (c >= 2) HGB_CUDA(cudaStreamWaitEvent(sc, P.ev_out[b], 0));
+        const int nrow = k.v1 - k.v0;
+        const size_t first = (size_t)(k.v0 - k.s0 + sub->halo) * sub->dp + kLead - p;
+        HGB_CUDA(cudaMemcpy2DAsync(P.dout[b], hp * sizeof(double), s.img[sub->cur] + first, sub->dp * sizeof(double),
+                                   hp * sizeof(double), nrow, cudaMemcpyDeviceToDevice, sc));
+        if (prev)
+            HGB_CUDA(cudaMemcpy2DAsync(P.dprev[b], hp * sizeof(double), s.img[sub->cur ^ 1] + first, sub->dp * sizeof(double),
+                                       hp * sizeof(double), nrow, cudaMemcpyDeviceToDevice, sc));
+        HGB_CUDA(cudaEventRecord(P.ev_res[b], sc));
+        HGB_CUDA(cudaStreamWaitEvent(P.s_out, P.ev_res[b], 0));
+        HGB_CUDA(cudaMemcpyAsync(cur + (size_t)k.v0 * hp, P.dout[b], (size_t)nrow * hp * sizeof(double), cudaMemcpyDeviceToHost, P.s_out));
+        if (prev)
+            HGB_CUDA(cudaMemcpyAsync(prev + (size_t)k.v0 * hp, P.dprev[b], (size_t)nrow * hp * sizeof(double), cudaMemcpyDeviceToHost, P.s_out));
+        HGB_CUDA(cudaEventRecord(P.ev_out[b], P.s_out));
+    }
+    HGB_CUDA(cudaStreamSynchronize(P.s_out));
+    HGB_CUDA(cudaStreamSynchronize(P.s_in));
+    HGB_CUDA(cudaGetLastError());
+    return HGB_OK;
+}
+
 int hgb_conv_run(double *cur, double *prev, int inner_w, int inner_h, int padding,
                  const double *kernel, int kw, int kh, int iterations, int ngpus) {
     HGB_ARG(iterations >= 0, "negative iteration count");
@@ -700,17 +920,24 @@ int hgb_conv_run(double *cur, double *prev, int inner_w, int inner_h, int paddin
     HGB_ARG(kernel && kw >= 1 && kh >= 1, "kernel");
     HGB_ARG(kw <= 2 * padding + 1 && kh <= 2 * padding + 1, "kernel larger than 2*padding+1");
     if (iterations == 0) return HGB_OK;         // the reference's loop body never runs
-    HGB_ARG(cur && prev, "NULL image");
+    HGB_ARG(cur, "NULL image");                 // prev == NULL: the caller does not want state n-1 back
+    if (g_cv_mode < 0) {
+        const char *e = getenv("HGB_CONV_FAST");
+        g_cv_mode = (e && atoi(e) != 0) ? HGB_CONV_FAST : HGB_CONV_EXACT;
+    }
+    int Hs = 0;
+    if (stream_plan(inner_w, inner_h, padding, iterations, g, prev, &Hs)) {
+        hgb_conv_destroy(g_cv);   // the two paths do not keep two images' worth of device memory around
+        g_cv = nullptr;
+        const int rc = conv_run_streamed(cur, prev, inner_w, inner_h, padding, kernel, kw, kh, iterations, Hs);
+        if (rc != HGB_ERR_STATE) return rc;     // HGB_ERR_STATE: the buffers could not be page-locked -> one piece
+    }
     if (!g_cv || g_cv_key[0] != inner_w || g_cv_key[1] != inner_h || g_cv_key[2] != padding ||
         g_cv_key[3] != g) {
         hgb_conv_destroy(g_cv);
         g_cv = nullptr;
         HGB_TRY(hgb_conv_create(&g_cv, inner_w, inner_h, padding, g));
         g_cv_key[0] = inner_w; g_cv_key[1] = inner_h; g_cv_key[2] = padding; g_cv_key[3] = g;
-    }
-    if (g_cv_mode < 0) {
-        const char *e = getenv("HGB_CONV_FAST");
-        g_cv_mode = (e && atoi(e) != 0) ? HGB_CONV_FAST : HGB_CONV_EXACT;
     }
     g_cv->uploaded = false;   // a new image follows: the mode may change
     HGB_TRY(hgb_conv_set_mode(g_cv, g_cv_mode));
@@ -727,5 +954,6 @@ namespace hgb {
 void conv_drop_cache() {
     hgb_conv_destroy(g_cv);
     g_cv = nullptr;
+    pipe_free();
 }
 }  // namespace hgb

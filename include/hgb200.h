@@ -175,6 +175,14 @@ int hgb_conv_run(double *cur, double *prev, int inner_w, int inner_h, int paddin
                  const double *kernel, int kw, int kh, int iterations, int ngpus);
 /* arithmetic mode of hgb_conv_run (default HGB_CONV_EXACT; env HGB_CONV_FAST=1 selects FAST) */
 int hgb_set_conv_mode(int mode);
+/* hgb_conv_run on one GPU streams tall images in row chunks so that the PCIe copies run under the
+ * iterations of other chunks (bit-identical: chunks overlap by iterations*padding rows).  `prev` may be
+ * NULL when state n-1 is not wanted (halves the device-to-host traffic).  chunk_rows: 0 = never stream,
+ * 1 = automatic (default; env HGB_CONV_STREAM_ROWS), else valid rows per chunk.  Asynchronous copies need
+ * page-locked memory: buffers that are not page-locked yet are registered (cudaHostRegister) and stay so
+ * across calls; call hgb_conv_unpin() (or hgb_finalize()) BEFORE freeing them. */
+int hgb_set_conv_streaming(int chunk_rows);
+int hgb_conv_unpin(void);
 
 /* ---- convolution: device-resident ------------------------------------- */
 typedef struct hgb_conv hgb_conv;

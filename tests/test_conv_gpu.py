@@ -438,3 +438,49 @@ def test_fast_mode_row_bands_agree_with_one_gpu(hgb, monkeypatch):
             cv.set_exchange(hgb.EXCHANGE_P2P).set_mode(hgb.CONV_FAST).set_kernel(kern).upload(img)
             cv.step(it)
             assert np.array_equal(cv.download(), want), g
+
+
+# ---- hgb_conv_run streamed in row chunks (PCIe copies under the iterations) --------------------------------
+@pytest.mark.parametrize("w,h,k,it,chunk", [(300, 1100, 3, 4, 128), (513, 1300, 7, 3, 200), (260, 2049, 5, 5, 300),
+                                            (64, 700, 3, 11, 100), (1000, 900, 3, 2, 250)])
+def test_streamed_run_is_bit_identical_to_the_oracle(hgb, w, h, k, it, chunk):
+    from oracle import port
+    p = k // 2
+    kern = synth.kernel_dense(k)
+    img = synth.add_padding(synth.image_float(w, h, seed=w + h + k), p)
+    want_c, want_p = img.copy(), np.zeros_like(img)
+    port.conv_run(want_c, want_p, w, h, p, kern, it)
+    try:
+        hgb.convolution.set_streaming(chunk)
+        cur, prev = img.copy(), np.full_like(img, -1.0)       # pageable memory: registered by the library
+        hgb.convolution.run_flat(cur, prev, w, h, p, kern, it)
+        assert np.array_equal(cur, want_c) and np.array_equal(prev, want_p)
+        cur2 = img.copy()
+        hgb.convolution.run_flat(cur2, None, w, h, p, kern, it)    # state n-1 not wanted
+        assert np.array_equal(cur2, want_c)
+        hgb.convolution.set_streaming(0)                           # one piece: same bits
+        cur3, prev3 = img.copy(), np.zeros_like(img)
+        hgb.convolution.run_flat(cur3, prev3, w, h, p, kern, it)
+        assert np.array_equal(cur3, want_c) and np.array_equal(prev3, want_p)
+    finally:
+        hgb.convolution.set_streaming(1)
+        hgb.convolution.unpin()
+
+
+def test_streamed_run_keeps_the_drop_in_semantics(hgb):
+    """run_on_padded_image through the streamed path: newest state in padded_img[0], the one before in buffer[0]"""
+    from oracle import port
+    w, h, p, it = 200, 1500, 1, 3
+    kern = synth.kernel_dense(3)
+    dense = synth.image_float(w, h, seed=77)
+    img = synth.add_padding(dense, p)
+    want_c, want_p = img.copy(), np.zeros_like(img)
+    port.conv_run(want_c, want_p, w, h, p, kern, it)
+    try:
+        hgb.convolution.set_streaming(100)
+        cur, prev = img.copy(), np.zeros_like(img)
+        hgb.convolution.run_flat(cur, prev, w, h, p, kern, it)
+        assert np.array_equal(cur, want_c) and np.array_equal(prev, want_p)
+    finally:
+        hgb.convolution.set_streaming(1)
+        hgb.convolution.unpin()
