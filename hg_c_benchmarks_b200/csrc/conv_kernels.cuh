@@ -594,4 +594,16 @@ conv_checksum_seq_kernel(const double *__restrict__ img, BandGeom g, double carr
     if (lane == 0) result[0] = val;
 }
 
+// rows of `cols` doubles from pitch `sp` to pitch `dp_` (both in doubles): the streamed drop-in moves row
+// chunks between its staging buffers (host pitch) and the image (device pitch) with SMs, so that the
+// copy engines stay free for the PCIe transfers running beside it
+__global__ void __launch_bounds__(256)
+conv_copy_rows_kernel(double *__restrict__ dst, size_t dp_, const double *__restrict__ src, size_t sp, int cols, int rows) {
+    for (int r = blockIdx.y; r < rows; r += gridDim.y) {
+        const double *s = src + (size_t)r * sp;
+        double *d = dst + (size_t)r * dp_;
+        for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < cols; c += gridDim.x * blockDim.x) d[c] = s[c];
+    }
+}
+
 }  // namespace hgb

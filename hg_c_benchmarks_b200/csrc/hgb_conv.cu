@@ -138,7 +138,10 @@ static int launch_stream(const hgb_conv *h, const CvShard &s, const double *in, 
 static int launch_fused2(const hgb_conv *h, const CvShard &s, const double *in, double *out, int crow0,
                          int crows, cudaStream_t st) {
     if (crows <= 0) return HGB_OK;
-    int chunk = h->chunk > 0 ? h->chunk : 64;   // measured on B200: profiles/r1c_conv3_fused_sweep.txt
+    // rows per CTA, measured on B200: 64 on a 16384-row image (profiles/r1c_conv3_fused_sweep.txt); on the
+    // 2048-row band of an 8-way split 64 leaves 1.56 waves of long CTAs (1.20 x an eighth of the full image),
+    // 48 gives 1.09 x (profiles/r2q_conv_band_sweep.txt): shorter CTAs, shorter tail
+    int chunk = h->chunk > 0 ? h->chunk : (crows <= 4096 ? 48 : 64);
     if (chunk > crows) chunk = crows;
     BandGeom g = geom(h, s);
     g.crow0 = crow0;
@@ -792,6 +795,12 @@ int pipe_setup(int W, int Hs, int p) {
     return HGB_OK;
 }
 
+void copy_rows(double *dst, size_t dpitch, const double *src, size_t spitch, int cols, int rows, cudaStream_t st) {
+    if (rows <= 0) return;
+    dim3 grid((unsigned)std::min((cols + 255) / 256, 64), (unsigned)std::min(rows, 1024));
+    conv_copy_rows_kernel<<<grid, 256, 0, st>>>(dst, dpitch, src, spitch, cols, rows);
+}
+
 static int g_stream_rows = -1;   // -1: HGB_CONV_STREAM_ROWS from the environment (0 = off); else rows per chunk
 }  // namespace
 
@@ -866,8 +875,8 @@ static int conv_run_streamed(double *cur, double *prev, int W, int H, int p, con
             const Chunk &q = chunks[c - 1];
             const int have1 = q.s0 + Hs;
             if (have1 > k.s0) {
-                HGB_CUDA(cudaMemcpyAsync(P.din[b], P.din[b ^ 1] + (size_t)(k.s0 - q.s0) * hp,
-                                         (size_t)(have1 - k.s0) * hp * sizeof(double), cudaMemcpyDeviceToDevice, P.s_in));
+                copy_rows(P.din[b], hp, P.din[b ^ 1] + (size_t)(k.s0 - q.s0) * hp, hp, (int)hp, have1 - k.s0, P.s_in);
+                HGB_LAUNCHED();
                 fresh0 = have1;
             }
         }
@@ -884,8 +893,8 @@ static int conv_run_streamed(double *cur, double *prev, int W, int H, int p, con
         if (c + 1 < nc) HGB_TRY(enqueue_h2d(c + 1));
         // the chunk becomes state 0 of the sub-handle (device-to-device, host pitch -> device pitch)
         HGB_CUDA(cudaStreamWaitEvent(sc, P.ev_in[b], 0));
-        HGB_CUDA(cudaMemcpy2DAsync(s.img[0] + (size_t)sub->halo * sub->dp + kLead - p, sub->dp * sizeof(double), P.din[b],
-                                   hp * sizeof(double), hp * sizeof(double), Hs, cudaMemcpyDeviceToDevice, sc));
+        copy_rows(s.img[0] + (size_t)sub->halo * sub->dp + kLead - p, sub->dp, P.din[b], hp, (int)hp, Hs, sc);
+        HGB_LAUNCHED();
         HGB_CUDA(cudaEventRecord(P.ev_loaded[b], sc));
         sub->cur = 0; sub->uploaded = true; sub->valid_xr = sub->halo; sub->integer_input = false;
         HGB_TRY(hgb_conv_step(sub, iterations, nullptr));
@@ -893,11 +902,12 @@ static int conv_run_streamed(double *cur, double *prev, int W, int H, int p, con
         if (c >= 2) HGB_CUDA(cudaStreamWaitEvent(sc, P.ev_out[b], 0));
         const int nrow = k.v1 - k.v0;
         const size_t first = (size_t)(k.v0 - k.s0 + sub->halo) * sub->dp + kLead - p;
-        HGB_CUDA(cudaMemcpy2DAsync(P.dout[b], hp * sizeof(double), s.img[sub->cur] + first, sub->dp * sizeof(double),
-                                   hp * sizeof(double), nrow, cudaMemcpyDeviceToDevice, sc));
-        if (prev)
-            HGB_CUDA(cudaMemcpy2DAsync(P.dprev[b], hp * sizeof(double), s.img[sub->cur ^ 1] + first, sub->dp * sizeof(double),
-                                       hp * sizeof(double), nrow, cudaMemcpyDeviceToDevice, sc));
+        copy_rows(P.dout[b], hp, s.img[sub->cur] + first, sub->dp, (int)hp, nrow, sc);
+        HGB_LAUNCHED();
+        if (prev) {
+            copy_rows(P.dprev[b], hp, s.img[sub->cur ^ 1] + first, sub->dp, (int)hp, nrow, sc);
+            HGB_LAUNCHED();
+        }
         HGB_CUDA(cudaEventRecord(P.ev_res[b], sc));
         HGB_CUDA(cudaStreamWaitEvent(P.s_out, P.ev_res[b], 0));
         HGB_CUDA(cudaMemcpyAsync(cur + (size_t)k.v0 * hp, P.dout[b], (size_t)nrow * hp * sizeof(double), cudaMemcpyDeviceToHost, P.s_out));
