@@ -7,6 +7,7 @@
 #include "nbody_kernels.cuh"
 #include "nbody_sym.cuh"
 #include "nbody_tri.cuh"
+#include "nbody_crow.cuh"
 
 using namespace hgb;
 
@@ -122,7 +123,13 @@ static bool g_default_sym_auto = false;                    // HGB_NBODY_SYM unse
 constexpr int kSymDefaultVariant = 242;                    // R = 2, U = 4, 2 CTAs (8 warps) per SM: profiles/r1e_nbody_sym_sweep_*.txt
 constexpr int kSymDefaultMinN = 393216;                    // measured: slower than the standard kernel at 2^18, 26 % faster at 2^19
 
-static bool tri_variant(int v) { return v >= 2001 && v <= 2013 && (v % 10) >= 1 && (v % 10) <= 3; }   // 200C / 201C (profiling)
+// third generation (nbody_crow.cuh, a CTA of W warps per row): 30PC (W = 4) / 31PC (W = 8), P = profiling, C = CTAs per SM
+static bool crow_variant(int v) {
+    const int c = v % 10, p = v / 10 % 10, w = v / 100 % 10;
+    return v >= 3001 && v <= 3112 && p <= 1 && ((w == 0 && (c == 1 || c == 2)) || (w == 1 && c == 1));
+}
+// second or third generation: 200C / 201C (profiling), or a cooperative-row variant (same buffers, plan and multi-GPU dealing)
+static bool tri_variant(int v) { return (v >= 2001 && v <= 2013 && (v % 10) >= 1 && (v % 10) <= 3) || crow_variant(v); }
 
 static bool sym_variant_known(int v) {
     if (tri_variant(v)) return true;
@@ -333,6 +340,21 @@ static int tri_shards_on_device(const hgb_nbody *h, const NbShard &s) {
     return c;
 }
 
+template <int W, int CTAS, bool PROF>
+static int launch_crow_variant(const TriArgs &a, int grid, cudaStream_t st) {
+    auto kern = nbody_crow_kernel<W, CTAS, PROF>;
+    static bool attr_done[16] = {false};   // per device: the attribute belongs to the function ON a device
+    int dev = 0;
+    HGB_CUDA(cudaGetDevice(&dev));
+    if (!attr_done[dev & 15]) {
+        HGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)crow_smem_bytes<W>()));
+        attr_done[dev & 15] = true;
+    }
+    kern<<<grid, W * 32, crow_smem_bytes<W>(), st>>>(a);
+    HGB_LAUNCHED();
+    return HGB_OK;
+}
+
 template <int CTAS, bool PROF>
 static int launch_tri_variant(const TriArgs &a, int grid, cudaStream_t st) {
     auto kern = nbody_tri_kernel<CTAS, PROF>;
@@ -401,6 +423,17 @@ static int launch_tri_step(hgb_nbody *h, int variant, int cur, int nxt) {
         a.racc = s.tri_racc; a.epoch_tag = epoch_tag; a.ctl = s.tri_ctl; a.spin_limit = kTriSpinLimit;
         const int grid = std::max(1, s.dev->sms * ctas / tri_shards_on_device(h, s));
         int rc = HGB_ERR_ARG;
+        if (crow_variant(variant)) {
+            switch (variant) {
+                case 3001: rc = launch_crow_variant<4, 1, false>(a, grid, s.dev->stream); break;
+                case 3002: rc = launch_crow_variant<4, 2, false>(a, grid, s.dev->stream); break;
+                case 3011: rc = launch_crow_variant<4, 1, true>(a, grid, s.dev->stream); break;
+                case 3012: rc = launch_crow_variant<4, 2, true>(a, grid, s.dev->stream); break;
+                case 3101: rc = launch_crow_variant<8, 1, false>(a, grid, s.dev->stream); break;
+                case 3111: rc = launch_crow_variant<8, 1, true>(a, grid, s.dev->stream); break;
+                default: set_error("no nbody_crow variant %d", variant);
+            }
+        } else
         switch (ctas * 2 + (prof ? 1 : 0)) {
             case 2: rc = launch_tri_variant<1, false>(a, grid, s.dev->stream); break;
             case 3: rc = launch_tri_variant<1, true>(a, grid, s.dev->stream); break;
@@ -531,7 +564,10 @@ int hgb_nbody_describe(const hgb_nbody *h, char *buf, int capacity) {
     char kern[160];
     const bool fast = h->mode == HGB_NBODY_FAST;
     const int v = sym_variant_in_effect(h);
-    if (tri_variant(v)) {
+    if (crow_variant(v)) {
+        snprintf(kern, sizeof kern, "nbody_crow_kernel<%d,%d> seg=%d rows=%d weight=%d", v / 100 % 10 ? 8 : 4, v % 10, h->tri_seg > 0 ? h->tri_seg : kTriDefaultSeg,
+                 h->tri_rows > 0 ? h->tri_rows : tri_default_rows(h), h->tri_weight > 0 ? h->tri_weight : tri_default_weight(h));
+    } else if (tri_variant(v)) {
         snprintf(kern, sizeof kern, "nbody_tri_kernel<%d> seg=%d rows=%d weight=%d", v % 10, h->tri_seg > 0 ? h->tri_seg : kTriDefaultSeg,
                  h->tri_rows > 0 ? h->tri_rows : tri_default_rows(h), h->tri_weight > 0 ? h->tri_weight : tri_default_weight(h));
     } else if (v) {

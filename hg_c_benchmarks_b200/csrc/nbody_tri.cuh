@@ -76,14 +76,15 @@ template <bool ALLV>
 __device__ __forceinline__ void forces_and_column(double px, double py, double pz, const double (&xj)[8],
                                                   const double (&yj)[8], const double (&zj)[8],
                                                   double (&vx)[8], double (&vy)[8], double (&vz)[8],
-                                                  unsigned &key, const double *col, double &chain, int cnt) {
+                                                  unsigned &key, const double *col, double &chain, int cnt, bool act) {
     constexpr int P = 8;
     double t[P], y[P], g[P], s[P], a[P], e[P], p[P], q[P];
     int ct = 0;   // column pairs consumed so far (compile-time after unrolling)
     auto column = [&](int pairs) {
 #pragma unroll
         for (int w = 0; w < pairs; ++w, ++ct) {
-            const double2 v = *reinterpret_cast<const double2 *>(col + 2 * ct);
+            double2 v = make_double2(0.0, 0.0);
+            if (act) v = *reinterpret_cast<const double2 *>(col + 2 * ct);   // lanes 24..31 own no chain: no load, no shared-memory wavefront
             if (ALLV || 2 * ct < cnt) chain = __dsub_rn(chain, v.x);
             if (ALLV || 2 * ct + 1 < cnt) chain = __dsub_rn(chain, v.y);
         }
@@ -303,7 +304,7 @@ nbody_tri_kernel(const __grid_constant__ TriArgs a) {
                 double chain = wait_word(w, at);
                 if (refill) w = ll_load(refill);
                 double vx[8], vy[8], vz[8];
-                forces_and_column<ALLV>(px, py, pz, xj, yj, zj, vx, vy, vz, key, col_prev, chain, cnt);
+                forces_and_column<ALLV>(px, py, pz, xj, yj, zj, vx, vy, vz, key, col_prev, chain, cnt, lane < 24);
                 if (decltype(fetch)::value) fetch_sources(m + 1);
                 row_pass(mine, vx, vy, vz);
                 publish(const_cast<ulonglong2 *>(at) + to_pub, chain);
