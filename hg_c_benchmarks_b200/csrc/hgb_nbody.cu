@@ -125,11 +125,12 @@ constexpr int kSymDefaultMinN = 393216;                    // measured: slower t
 
 // third generation (nbody_crow.cuh, a CTA of W warps per row): 30PC (W = 4) / 31PC (W = 8), P = profiling, C = CTAs per SM
 static bool crow_variant(int v) {
-    const int c = v % 10, p = v / 10 % 10, w = v / 100 % 10;
-    return v >= 3001 && v <= 3112 && p <= 1 && ((w == 0 && (c == 1 || c == 2)) || (w == 1 && c == 1));
+    const int c = v % 10, p = v / 10 % 10, w = v / 100 % 10;   // p: 1 profiling, 2 row pass fused into the next force block, 3 both
+    return v >= 3001 && v <= 3132 && p <= 3 && ((w == 0 && (c == 1 || c == 2)) || (w == 1 && c == 1 && p <= 1));
 }
 // second or third generation: 200C / 201C (profiling), or a cooperative-row variant (same buffers, plan and multi-GPU dealing)
-static bool tri_variant(int v) { return (v >= 2001 && v <= 2013 && (v % 10) >= 1 && (v % 10) <= 3) || crow_variant(v); }
+// 202C: row pass fused into the next minitile's force block (ROWPIPE)
+static bool tri_variant(int v) { return (v >= 2001 && v <= 2023 && (v % 10) >= 1 && (v % 10) <= 3) || crow_variant(v); }
 
 static bool sym_variant_known(int v) {
     if (tri_variant(v)) return true;
@@ -340,9 +341,9 @@ static int tri_shards_on_device(const hgb_nbody *h, const NbShard &s) {
     return c;
 }
 
-template <int W, int CTAS, bool PROF>
+template <int W, int CTAS, bool PROF, bool ROWPIPE = false>
 static int launch_crow_variant(const TriArgs &a, int grid, cudaStream_t st) {
-    auto kern = nbody_crow_kernel<W, CTAS, PROF>;
+    auto kern = nbody_crow_kernel<W, CTAS, PROF, ROWPIPE>;
     static bool attr_done[16] = {false};   // per device: the attribute belongs to the function ON a device
     int dev = 0;
     HGB_CUDA(cudaGetDevice(&dev));
@@ -355,9 +356,9 @@ static int launch_crow_variant(const TriArgs &a, int grid, cudaStream_t st) {
     return HGB_OK;
 }
 
-template <int CTAS, bool PROF>
+template <int CTAS, bool PROF, bool ROWPIPE = false>
 static int launch_tri_variant(const TriArgs &a, int grid, cudaStream_t st) {
-    auto kern = nbody_tri_kernel<CTAS, PROF>;
+    auto kern = nbody_tri_kernel<CTAS, PROF, ROWPIPE>;
     static bool attr_done[16] = {false};   // per device: the attribute belongs to the function ON a device
     int dev = 0;
     HGB_CUDA(cudaGetDevice(&dev));
@@ -385,7 +386,7 @@ static int launch_tri_step(hgb_nbody *h, int variant, int cur, int nxt) {
     const unsigned epoch_tag = (step % 2047 + 1) << 21;
     const int seg = h->sh[0].tri_plan_seg, rows = h->sh[0].tri_plan_rows, T = (h->n + 31) / 32;
     const int ctas = variant % 10;
-    const bool prof = (variant / 10) % 10 == 1;
+    const bool prof = (variant / 10) % 10 == 1 || (variant / 10) % 10 == 3;
     for (NbShard &s : h->sh) {
         HGB_CUDA(cudaSetDevice(s.dev->device));
         HGB_CUDA(cudaMemsetAsync(s.tri_ctl, 0, sizeof(int), s.dev->stream));                           // ticket
@@ -429,9 +430,21 @@ static int launch_tri_step(hgb_nbody *h, int variant, int cur, int nxt) {
                 case 3002: rc = launch_crow_variant<4, 2, false>(a, grid, s.dev->stream); break;
                 case 3011: rc = launch_crow_variant<4, 1, true>(a, grid, s.dev->stream); break;
                 case 3012: rc = launch_crow_variant<4, 2, true>(a, grid, s.dev->stream); break;
+                case 3021: rc = launch_crow_variant<4, 1, false, true>(a, grid, s.dev->stream); break;
+                case 3022: rc = launch_crow_variant<4, 2, false, true>(a, grid, s.dev->stream); break;
+                case 3031: rc = launch_crow_variant<4, 1, true, true>(a, grid, s.dev->stream); break;
+                case 3032: rc = launch_crow_variant<4, 2, true, true>(a, grid, s.dev->stream); break;
                 case 3101: rc = launch_crow_variant<8, 1, false>(a, grid, s.dev->stream); break;
                 case 3111: rc = launch_crow_variant<8, 1, true>(a, grid, s.dev->stream); break;
                 default: set_error("no nbody_crow variant %d", variant);
+            }
+        } else
+        if ((variant / 10) % 10 == 2) {
+            switch (ctas) {
+                case 1: rc = launch_tri_variant<1, false, true>(a, grid, s.dev->stream); break;
+                case 2: rc = launch_tri_variant<2, false, true>(a, grid, s.dev->stream); break;
+                case 3: rc = launch_tri_variant<3, false, true>(a, grid, s.dev->stream); break;
+                default: set_error("no nbody_tri variant %d", variant);
             }
         } else
         switch (ctas * 2 + (prof ? 1 : 0)) {
@@ -565,10 +578,10 @@ int hgb_nbody_describe(const hgb_nbody *h, char *buf, int capacity) {
     const bool fast = h->mode == HGB_NBODY_FAST;
     const int v = sym_variant_in_effect(h);
     if (crow_variant(v)) {
-        snprintf(kern, sizeof kern, "nbody_crow_kernel<%d,%d> seg=%d rows=%d weight=%d", v / 100 % 10 ? 8 : 4, v % 10, h->tri_seg > 0 ? h->tri_seg : kTriDefaultSeg,
+        snprintf(kern, sizeof kern, "nbody_crow_kernel<%d,%d%s> seg=%d rows=%d weight=%d", v / 100 % 10 ? 8 : 4, v % 10, (v / 10) % 10 >= 2 ? ",rowpipe" : "", h->tri_seg > 0 ? h->tri_seg : kTriDefaultSeg,
                  h->tri_rows > 0 ? h->tri_rows : tri_default_rows(h), h->tri_weight > 0 ? h->tri_weight : tri_default_weight(h));
     } else if (tri_variant(v)) {
-        snprintf(kern, sizeof kern, "nbody_tri_kernel<%d> seg=%d rows=%d weight=%d", v % 10, h->tri_seg > 0 ? h->tri_seg : kTriDefaultSeg,
+        snprintf(kern, sizeof kern, "nbody_tri_kernel<%d%s> seg=%d rows=%d weight=%d", v % 10, (v / 10) % 10 == 2 ? ",rowpipe" : "", h->tri_seg > 0 ? h->tri_seg : kTriDefaultSeg,
                  h->tri_rows > 0 ? h->tri_rows : tri_default_rows(h), h->tri_weight > 0 ? h->tri_weight : tri_default_weight(h));
     } else if (v) {
         snprintf(kern, sizeof kern, "nbody_sym_kernel<%d,%d,%d>", v / 100, v / 10 % 10, v % 10);

@@ -77,7 +77,9 @@ __device__ __noinline__ void crow_wait(const TriArgs &a, unsigned bar, unsigned 
 // W warps per row (a multiple of 4: a warp's minitiles then sit at a fixed place inside the 32-source chunks of
 // the chain-word layout), CTAS resident CTAs per SM.  PROF: lane 0 of every warp accumulates clock64 spans in
 // ctl[8..] (chain-word waits, row-accumulator waits, items, triangles, item count, token waits).
-template <int W, int CTAS, bool PROF = false>
+// ROWPIPE: the ordered adds of a minitile are fused into the force block of the warp's NEXT minitile
+// (forces_column_row): the token is taken at the start of that block and handed on after its first stages.
+template <int W, int CTAS, bool PROF = false, bool ROWPIPE = false>
 __global__ void __launch_bounds__(W * 32, CTAS)
 nbody_crow_kernel(const __grid_constant__ TriArgs a) {
     static_assert(W % 4 == 0 && W >= 4, "warps per row");
@@ -237,6 +239,75 @@ nbody_crow_kernel(const __grid_constant__ TriArgs a) {
                 publish(const_cast<ulonglong2 *>(at) + to_pub, chain);
                 __syncwarp();   // column lanes read these values during the next minitile; ring slot hand-over
             };
+            if constexpr (ROWPIPE) {
+                double vxa[8], vya[8], vza[8], vxb[8], vyb[8], vzb[8];   // values of this warp's minitiles, alternating
+                auto store_tb = [&](double *mine, const double (&vx)[8], const double (&vy)[8], const double (&vz)[8]) {
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        mine[u * kTbPitch] = vx[u]; mine[(8 + u) * kTbPitch] = vy[u]; mine[(16 + u) * kTbPitch] = vz[u];
+                    }
+                };
+                // this warp's minitile i >= 1: its forces, the column pass AND the ordered adds of its minitile i-1
+                auto block_p = [&](int i, ulonglong2 &w, const ulonglong2 *at, const double *col_prev, double *mine, bool more,
+                                   const double (&ox)[8], const double (&oy)[8], const double (&oz)[8],
+                                   double (&nx)[8], double (&ny)[8], double (&nz)[8]) {
+                    double chain = wait_word(w, at);
+                    if (more) w = ll_load(at + 2 * WS);
+                    take_token(q + W * (i - 1));
+                    forces_column_row<ALLV>(px, py, pz, xj, yj, zj, nx, ny, nz, key, col_prev, chain, cnt, lane < 24,
+                                            ox, oy, oz, ax, ay, az, [&] { give_token(); });
+                    if (more) fetch_sources(i + 1);
+                    store_tb(mine, nx, ny, nz);
+                    publish(const_cast<ulonglong2 *>(at) + to_pub, chain);
+                    __syncwarp();
+                };
+                {   // minitile 0
+                    fetch_sources(0);
+                    next_chunk(0);
+                    double qx[8], qy[8], qz[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) { qx[u] = px; qy[u] = py; qz[u] = pz; }
+                    pair_forces<8>(qx, qy, qz, xj, yj, zj, vxa, vya, vza, key);
+                    if (C > 1) fetch_sources(1);
+                    store_tb(tb0, vxa, vya, vza);
+                    __syncwarp();
+                }
+                int i = 1;
+#pragma unroll 1
+                for (; i + 1 < C; i += 2) {
+                    check_range();
+                    block_p(i, we, wp, col0, tb1, true, vxa, vya, vza, vxb, vyb, vzb);
+                    if ((i & 3) == 3) next_chunk((i + 1) >> 2);
+                    block_p(i + 1, wo, wp + WS, col1, tb0, i + 2 < C, vxb, vyb, vzb, vxa, vya, vza);
+                    wp += 2 * WS;
+                }
+                check_range();
+                const double *col_last = col0;
+                if (i < C) {   // one odd minitile left; its values move to the first set (once per item)
+                    block_p(i, we, wp, col0, tb1, false, vxa, vya, vza, vxb, vyb, vzb);
+                    wp += WS;
+                    col_last = col1;
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) { vxa[u] = vxb[u]; vya[u] = vyb[u]; vza[u] = vzb[u]; }
+                }
+                // ordered adds and column pass of this warp's last minitile C-1
+                take_token(q + W * (C - 1));
+#pragma unroll
+                for (int u = 0; u < 8; ++u) { ax = __dadd_rn(ax, vxa[u]); ay = __dadd_rn(ay, vya[u]); az = __dadd_rn(az, vza[u]); }
+                give_token();
+                double chain = wait_word(col_last == col0 ? we : wo, wp);
+#pragma unroll
+                for (int tcol = 0; tcol < 16; ++tcol) {
+                    double2 v = make_double2(0.0, 0.0);
+                    if (lane < 24) v = *reinterpret_cast<const double2 *>(col_last + 2 * tcol);
+                    if (ALLV || 2 * tcol < cnt) chain = __dsub_rn(chain, v.x);
+                    if (ALLV || 2 * tcol + 1 < cnt) chain = __dsub_rn(chain, v.y);
+                }
+                check_range();
+                publish(const_cast<ulonglong2 *>(wp) + to_pub, chain);
+                __syncwarp();
+                return;
+            }
             {   // minitile 0: nothing before it to do a column pass for
                 fetch_sources(0);
                 next_chunk(0);

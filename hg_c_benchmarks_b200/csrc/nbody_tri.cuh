@@ -148,6 +148,92 @@ __device__ __forceinline__ void forces_and_column(double px, double py, double p
     static_assert(2 + 2 + 12 == 16, "16 column pairs = 32 targets");
 }
 
+// The same block with the ROW pass of the previous minitile fused in as well ("row pipelining"): `pvx/pvy/pvz`
+// are that minitile's 8 x 3 values, added to the row's sums in source order (reference src/nbody/nbody-run.c:19-21),
+// one source per stage of the force evaluation, so the 8-deep dependent add chains cost no issue time of their
+// own; `after_row()` runs right after the last add (the cooperative-row kernel hands the sums on there).
+template <bool ALLV, class AfterRow>
+__device__ __forceinline__ void forces_column_row(double px, double py, double pz, const double (&xj)[8],
+                                                  const double (&yj)[8], const double (&zj)[8],
+                                                  double (&vx)[8], double (&vy)[8], double (&vz)[8],
+                                                  unsigned &key, const double *col, double &chain, int cnt, bool act,
+                                                  const double (&pvx)[8], const double (&pvy)[8], const double (&pvz)[8],
+                                                  double &ax, double &ay, double &az, AfterRow after_row) {
+    constexpr int P = 8;
+    double t[P], y[P], g[P], s[P], a[P], e[P], p[P], q[P];
+    int ct = 0, ru = 0;   // column pairs / row sources consumed so far (compile-time after unrolling)
+    auto column = [&](int pairs) {
+#pragma unroll
+        for (int w = 0; w < pairs; ++w, ++ct) {
+            double2 v = make_double2(0.0, 0.0);
+            if (act) v = *reinterpret_cast<const double2 *>(col + 2 * ct);
+            if (ALLV || 2 * ct < cnt) chain = __dsub_rn(chain, v.x);
+            if (ALLV || 2 * ct + 1 < cnt) chain = __dsub_rn(chain, v.y);
+        }
+    };
+    auto row = [&]() {
+        ax = __dadd_rn(ax, pvx[ru]); ay = __dadd_rn(ay, pvy[ru]); az = __dadd_rn(az, pvz[ru]);
+        ++ru;
+    };
+#pragma unroll
+    for (int u = 0; u < P; ++u) { vx[u] = __dsub_rn(xj[u], px); vy[u] = __dsub_rn(yj[u], py); vz[u] = __dsub_rn(zj[u], pz); }
+    column(2); row();
+#pragma unroll
+    for (int u = 0; u < P; ++u) { s[u] = __dmul_rn(vx[u], vx[u]); a[u] = __dmul_rn(vy[u], vy[u]); e[u] = __dmul_rn(vz[u], vz[u]); }
+    column(2); row();
+#pragma unroll
+    for (int u = 0; u < P; ++u) s[u] = __dadd_rn(s[u], a[u]);
+    column(1); row();
+#pragma unroll
+    for (int u = 0; u < P; ++u) s[u] = __dadd_rn(s[u], e[u]);
+    column(1); row();
+#pragma unroll
+    for (int u = 0; u < P; ++u) s[u] = __dadd_rn(s[u], kEps);
+    column(1); row();
+#pragma unroll
+    for (int u = 0; u < P; ++u) t[u] = __dmul_rn(s[u], s[u]);
+    column(1); row();
+#pragma unroll
+    for (int u = 0; u < P; ++u) t[u] = __dmul_rn(t[u], s[u]);            // (s*s)*s
+    column(1); row();
+#pragma unroll
+    for (int u = 0; u < P; ++u) { y[u] = mufu_rsqrt(t[u]); key = max(key, range_key(t[u])); }
+#pragma unroll
+    for (int u = 0; u < P; ++u) a[u] = __dmul_rn(y[u], y[u]);
+    column(1); row();
+    after_row();
+#pragma unroll
+    for (int u = 0; u < P; ++u) e[u] = __fma_rn(t[u], -a[u], 1.0);
+    column(1);
+#pragma unroll
+    for (int u = 0; u < P; ++u) { p[u] = __fma_rn(e[u], 0.375, 0.5); q[u] = __dmul_rn(y[u], e[u]); }
+    column(1);
+#pragma unroll
+    for (int u = 0; u < P; ++u) y[u] = __fma_rn(p[u], q[u], y[u]);       // ~1/sqrt(t)
+    column(1);
+#pragma unroll
+    for (int u = 0; u < P; ++u) g[u] = __dmul_rn(t[u], y[u]);
+    column(1);
+#pragma unroll
+    for (int u = 0; u < P; ++u) e[u] = __fma_rn(-g[u], g[u], t[u]);
+    column(1);
+#pragma unroll
+    for (int u = 0; u < P; ++u) g[u] = __fma_rn(e[u], half_of(y[u]), g[u]);  // RN(sqrt(t))
+    column(1);
+#pragma unroll
+    for (int u = 0; u < P; ++u) y[u] = odd_up(y[u]);                     // see inv_sqrt_ieee
+#pragma unroll
+    for (int u = 0; u < P; ++u) e[u] = __fma_rn(y[u], -g[u], 1.0);
+#pragma unroll
+    for (int u = 0; u < P; ++u) y[u] = __fma_rn(y[u], e[u], y[u]);
+#pragma unroll
+    for (int u = 0; u < P; ++u) e[u] = __fma_rn(y[u], -g[u], 1.0);
+#pragma unroll
+    for (int u = 0; u < P; ++u) y[u] = __fma_rn(y[u], e[u], y[u]);       // RN(1/g)
+#pragma unroll
+    for (int u = 0; u < P; ++u) { vx[u] = __dmul_rn(vx[u], y[u]); vy[u] = __dmul_rn(vy[u], y[u]); vz[u] = __dmul_rn(vz[u], y[u]); }
+}
+
 // ---- cold paths, out of line: the hot loop must stay small (a 2^17-body profile of the first version showed
 // one "no instruction" stall per issued instruction: the unrolled cold code had pushed the loop out of the
 // instruction cache) ------------------------------------------------------------------------------------
@@ -186,7 +272,8 @@ __device__ __noinline__ ulonglong2 tri_poll(const TriArgs &a, const ulonglong2 *
 
 // CTAS resident CTAs per SM (register budget).  PROF: lane 0 of every warp accumulates clock64 spans
 // (waits for chain words, waits for row accumulators, whole items, the diagonal triangles) in ctl[8..].
-template <int CTAS, bool PROF = false>
+// ROWPIPE: the row pass of a minitile is fused into the force block of the NEXT one as well (forces_column_row).
+template <int CTAS, bool PROF = false, bool ROWPIPE = false>
 __global__ void __launch_bounds__(kTriWarps * 32, CTAS)
 nbody_tri_kernel(const __grid_constant__ TriArgs a) {
     constexpr unsigned FULL = 0xffffffffu;
@@ -310,6 +397,63 @@ nbody_tri_kernel(const __grid_constant__ TriArgs a) {
                 publish(const_cast<ulonglong2 *>(at) + to_pub, chain);
                 __syncwarp();   // column lanes read these values during the next minitile; ring slot hand-over
             };
+            if constexpr (ROWPIPE) {
+                // two sets of 8 x 3 values, alternating: a minitile's values are added to the row's sums during the next one
+                double vxa[8], vya[8], vza[8], vxb[8], vyb[8], vzb[8];
+                auto store_tb = [&](double *mine, const double (&vx)[8], const double (&vy)[8], const double (&vz)[8]) {
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        mine[u * kTbPitch] = vx[u]; mine[(8 + u) * kTbPitch] = vy[u]; mine[(16 + u) * kTbPitch] = vz[u];
+                    }
+                };
+                auto minitile_p = [&](int m, ulonglong2 &w, const ulonglong2 *at, const ulonglong2 *refill, const double *col_prev,
+                                      double *mine, auto fetch, const double (&ox)[8], const double (&oy)[8], const double (&oz)[8],
+                                      double (&nx)[8], double (&ny)[8], double (&nz)[8]) {
+                    double chain = wait_word(w, at);
+                    if (refill) w = ll_load(refill);
+                    forces_column_row<ALLV>(px, py, pz, xj, yj, zj, nx, ny, nz, key, col_prev, chain, cnt, lane < 24,
+                                            ox, oy, oz, ax, ay, az, [] {});
+                    if (decltype(fetch)::value) fetch_sources(m + 1);
+                    store_tb(mine, nx, ny, nz);
+                    publish(const_cast<ulonglong2 *>(at) + to_pub, chain);
+                    __syncwarp();
+                };
+                {   // minitile 0
+                    fetch_sources(0);
+                    next_chunk(0);
+                    double qx[8], qy[8], qz[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) { qx[u] = px; qy[u] = py; qz[u] = pz; }
+                    pair_forces<8>(qx, qy, qz, xj, yj, zj, vxa, vya, vza, key);
+                    fetch_sources(1);
+                    store_tb(tb0, vxa, vya, vza);
+                    __syncwarp();
+                }
+                int step = 16;
+#pragma unroll 1
+                for (int m = 1; m < M - 2; m += 2) {
+                    check_range();
+                    minitile_p(m, we, wp, wp + step, col0, tb1, std::true_type{}, vxa, vya, vza, vxb, vyb, vzb);
+                    if (step == 80) next_chunk((m + 1) >> 2);
+                    minitile_p(m + 1, wo, wp + 8, wp + step + 8, col1, tb0, std::true_type{}, vxb, vyb, vzb, vxa, vya, vza);
+                    wp += step;
+                    step = 96 - step;
+                }
+                check_range();
+                minitile_p(M - 1, we, wp, nullptr, col0, tb1, std::false_type{}, vxa, vya, vza, vxb, vyb, vzb);
+                double chain = wait_word(wo, wp + 8);
+#pragma unroll
+                for (int tcol = 0; tcol < 16; ++tcol) {   // row pass and column pass of the segment's last minitile
+                    const double2 v = *reinterpret_cast<const double2 *>(col1 + 2 * tcol);
+                    if (ALLV || 2 * tcol < cnt) chain = __dsub_rn(chain, v.x);
+                    if (ALLV || 2 * tcol + 1 < cnt) chain = __dsub_rn(chain, v.y);
+                    if (tcol < 8) { ax = __dadd_rn(ax, vxb[tcol]); ay = __dadd_rn(ay, vyb[tcol]); az = __dadd_rn(az, vzb[tcol]); }
+                }
+                check_range();
+                publish(const_cast<ulonglong2 *>(wp) + 8 + to_pub, chain);
+                __syncwarp();
+                return;
+            }
             {   // minitile 0: nothing before it to do a column pass for
                 fetch_sources(0);
                 next_chunk(0);

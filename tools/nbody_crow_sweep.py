@@ -29,7 +29,7 @@ def run(n, pos, variant, seg=0, steps=1, rows=0, weight=0):
         ms = nb.step(steps) / steps
         out = nb.download()
         counters = None
-        if variant >= 2000 and (variant // 10) % 10 == 1:
+        if variant >= 2000 and (variant // 10) % 10 in (1, 3):
             c = (C.c_ulonglong * 7)()
             H._abi.check(H.lib().hgb_nbody_sym_counters(nb._h, c))
             counters = list(c)
@@ -45,7 +45,10 @@ for n in sizes:
     print(f"n={n} sym 242              : {ms:9.3f} ms  {n * n / (ms * 1e-3):.4e} inter/s  same={np.array_equal(out, ref)}", flush=True)
     ms, out, _ = run(n, pos, 2002, 16384 if n > 16384 else 0, steps=steps, rows=8, weight=32)
     print(f"n={n} tri 2002 seg=16384 rows=8 weight=32: {ms:9.3f} ms  {n * n / (ms * 1e-3):.4e} inter/s  same={np.array_equal(out, ref)}", flush=True)
-    for variant, seg, rows, weight in grid:
+    for spec in grid:
+        variant, seg, rows, weight = spec[:4]
+        flags = spec[4] if len(spec) > 4 else 0
+        os.environ["HGB_NBODY_TRI_FLAGS"] = str(flags)      # read by the library at every launch
         if seg > n:
             continue
         ms, out, c = run(n, pos, variant, seg, steps=steps, rows=rows, weight=weight)
@@ -54,6 +57,6 @@ for n in sizes:
             tot = max(1, c[2])
             extra = (f"  waits: chain {100.0 * c[0] / tot:.1f} % racc {100.0 * c[1] / tot:.1f} % token {100.0 * c[5] / tot:.1f} % "
                      f"triangles {100.0 * c[3] / tot:.1f} %")
-        print(f"n={n} crow {variant} seg={seg:6d} rows={rows:3d} weight={weight:3d}: {ms:9.3f} ms  {n * n / (ms * 1e-3):.4e} inter/s  "
+        print(f"n={n} {'crow' if variant >= 3000 else 'tri '} {variant} seg={seg:6d} rows={rows:3d} weight={weight:3d} flags={flags}: {ms:9.3f} ms  {n * n / (ms * 1e-3):.4e} inter/s  "
               f"same={np.array_equal(out, ref)}{extra}", flush=True)
 H.lib().hgb_finalize()
