@@ -45,7 +45,7 @@ struct hgb_nbody {
     bool uploaded = false;
     bool dynamics = false;  // hgb_nbody_set_dynamics was called
     int sym = 0;            // pair-symmetric kernel variant R*100 + U*10 + CTAs/SM, or 2000 + CTAs/SM (0 = off)
-    bool sym_auto = false;  // the library picks the variant per GPU count (sym_variant_in_effect)
+    int sym_auto = 0;       // the library picks the variant per GPU count (sym_variant_in_effect)
     int sym_min_n = 0;      // ... used when n >= sym_min_n, EXACT mode
     int tri_seg = 0;        // second-generation kernel (variants 2000+): sources per segment,
     int tri_rows = 0;       // ... rows per tile,
@@ -163,15 +163,26 @@ static_assert((kSymMaxN / 32) < (1 << 21) + 1, "worker id must fit the 21-bit ta
 constexpr int kTriDefaultVariant = 2002;
 constexpr int kTriMinNPerGpu = 131072;
 
+// Automatic choice (HGB_NBODY_SYM unset or 1), measured on B200 (profiles/r3g_small_n.txt, r3c_*, r2j_*).  What
+// decides is the number of bodies per GPU: it sets how long the wavefronts' serial chains are against the work.
+//   one GPU:   n < 49 152 standard kernel | < 229 376 cooperative rows (nbody_crow_kernel: +19 % at 64k, +31 % at 96k)
+//              | < 786 432 one warp per row (nbody_tri_kernel: +33 % at 384k, 374 vs 405 ms at 512k)
+//              | else first generation (nbody_sym_kernel: 1410 vs 1474 ms at 2^20)
+//   g GPUs:    n / g < 65 536 standard kernel with ncclAllGather | < 262 144 cooperative rows | else one warp per row
+constexpr int kCrowDefaultVariant = 3002;
+static int auto_variant(const hgb_nbody *h) {
+    const long long per = h->n / h->world;
+    if (h->world == 1) return h->n >= 786432 ? kSymDefaultVariant : h->n >= 229376 ? kTriDefaultVariant : h->n >= 49152 ? kCrowDefaultVariant : 0;
+    return per >= 262144 ? kTriDefaultVariant : per >= 65536 ? kCrowDefaultVariant : 0;
+}
+
 // the pair-symmetric variant the next step of this handle runs (0 = the standard kernel)
 static int sym_variant_in_effect(const hgb_nbody *h) {
     if (h->sym == 0 || h->mode != HGB_NBODY_EXACT || h->n >= kSymMaxN) return 0;
-    int v = h->sym, min_n = h->sym_min_n;
-    if (h->sym_auto && h->world > 1) {
-        v = kTriDefaultVariant;
-        min_n = std::max(min_n, kTriMinNPerGpu * h->world);
-    }
-    if (h->n < min_n) return 0;
+    // sym_auto 2: the library's default (the whole ladder); 1: hgb_nbody_set_symmetric(h, 1, min_n) -- the first
+    // generation on one GPU from min_n up (what the caller asked for), the ladder across GPUs
+    const int v = (h->sym_auto == 2 || (h->sym_auto == 1 && h->world > 1)) ? auto_variant(h) : h->sym;
+    if (v == 0 || h->n < h->sym_min_n) return 0;
     if (!tri_variant(v)) return h->world == 1 ? v : 0;   // first generation: one GPU
     if (h->world == 1) return v;
     // rows dealt over GPUs: peer-mapped buffers -- of this process (peer-store handles) or of the other ranks (CUDA IPC)
@@ -537,11 +548,11 @@ static void sym_defaults(hgb_nbody *h) {
     }
     if (g_default_sym_min_n < 0) {
         const char *e = getenv("HGB_NBODY_SYM_MIN_N");
-        g_default_sym_min_n = e ? atoi(e) : kSymDefaultMinN;
+        g_default_sym_min_n = e ? atoi(e) : (g_default_sym_auto ? 0 : kSymDefaultMinN);   // automatic: the ladder above decides
         if (g_default_sym_min_n < 0) g_default_sym_min_n = 0;
     }
     h->sym = g_default_sym;
-    h->sym_auto = g_default_sym_auto;
+    h->sym_auto = g_default_sym_auto ? 2 : 0;
     h->sym_min_n = g_default_sym_min_n;
 }
 
@@ -555,7 +566,7 @@ int hgb_nbody_set_symmetric(hgb_nbody *h, int variant, int min_n) {
     HGB_ARG(variant == 0 || sym_variant_known(variant), "pair-symmetric variant (R*100 + U*10 + CTAs per SM, or 2000 + CTAs per SM)");
     HGB_ARG(min_n >= 0, "min_n");
     h->sym = variant;
-    h->sym_auto = automatic;
+    h->sym_auto = automatic ? 1 : 0;
     h->sym_min_n = min_n;
     return HGB_OK;
 }

@@ -162,17 +162,19 @@ def test_sym_is_ignored_where_it_does_not_apply(hgb):
 
 
 def test_sym_default_policy(hgb):
-    """new one-GPU handles use the symmetric kernel from n = 393216 up; an explicit hgb_nbody_tune
-    variant of the standard kernel, FAST mode or a small n switch it off"""
+    """new one-GPU handles pick the kernel by size (standard < 49152 <= cooperative rows < 229376 <= one warp
+    per row < 786432 <= first generation); an explicit hgb_nbody_tune variant of the standard kernel or FAST
+    mode switch the pair-symmetric kernels off; hgb_nbody_set_symmetric(h, 1, min_n) asks for the first generation"""
     L = hgb.lib()
     if os.environ.get("HGB_NBODY_SYM") or os.environ.get("HGB_NBODY_SYM_MIN_N"):
         pytest.skip("defaults overridden by the environment")
+    for n, want in ((49151, 0), (49152, 3002), (229375, 3002), (229376, 2002), (786431, 2002), (786432, 242)):
+        with hgb.nbody.NBody(n) as nb:
+            assert L.hgb_nbody_symmetric(nb._h) == want, n
     with hgb.nbody.NBody(393216) as nb:
-        assert L.hgb_nbody_symmetric(nb._h) == 242
         nb.tune(128, 2, 24)
         assert L.hgb_nbody_symmetric(nb._h) == 0
     with hgb.nbody.NBody(393215) as nb:
-        assert L.hgb_nbody_symmetric(nb._h) == 0
         nb.symmetric(1, 0)
         assert L.hgb_nbody_symmetric(nb._h) == 242
     with hgb.nbody.NBody(1 << 19, mode=hgb.NBODY_FAST) as nb:

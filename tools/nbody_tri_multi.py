@@ -28,7 +28,7 @@ def run(g, variant, seg=0, rows=0, weight=0, steps=2):
         ms = nb.step(steps) / steps
         out = nb.download()
         counters = None
-        if variant >= 2010:
+        if variant >= 2010 and (variant // 10) % 10 == 1:
             c = (C.c_ulonglong * 7)()
             H._abi.check(H.lib().hgb_nbody_sym_counters(nb._h, c))
             counters = list(c)
@@ -50,11 +50,14 @@ for g in gs:
     grid = [(2002, 16384, r, w) for r in (16, 32, 64) for w in (32, 64, 128, 256)] + [(2002, 8192, r, w) for r in (16, 32) for w in (64, 128)]
     if os.environ.get("TRI_GRID") == "small":
         grid = [(2002, 16384, 8, 32), (2002, 16384, 16, 32), (2002, 16384, 16, 64), (2002, 8192, 16, 32), (2003, 16384, 16, 32)]
+    if os.environ.get("TRI_GRID") == "crow":
+        grid = [(2002, 16384, 16, 64), (3002, 16384, 8, 32), (3002, 16384, 16, 64), (3002, 16384, 4, 16), (3002, 8192, 8, 32),
+                (3002, 16384, 8, 64), (3002, 32768, 8, 32)]
     for variant, seg, rows, weight in grid:
         ms, out, _, what = run(g, variant, seg, rows, weight)
         print(f"g={g} n={n} tri {variant} seg={seg:6d} rows={rows:3d} weight={weight:3d}: {ms:9.3f} ms  "
               f"{n * n / (ms * 1e-3):.4e} inter/s  same={np.array_equal(out, ref)}  [{what[0]}]", flush=True)
-    ms, out, c, _ = run(g, 2012, 16384, 16, 64, steps=1)
+    ms, out, c, _ = run(g, 3012 if os.environ.get("TRI_GRID") == "crow" else 2012, 16384, 16 if os.environ.get("TRI_GRID") != "crow" else 8, 64 if os.environ.get("TRI_GRID") != "crow" else 32, steps=1)
     tot = max(1, c[2])
     print(f"g={g} n={n} tri 2012 (profiling, shard 0): {ms:9.3f} ms; chain-word waits {100.0 * c[0] / tot:.1f} %, "
           f"row-accumulator waits {100.0 * c[1] / tot:.1f} %, items {c[4]}, cycles per item {tot / max(1, c[4]):.0f}", flush=True)
