@@ -48,6 +48,7 @@ SIGNATURES = {
     "hgb_nbody_set_symmetric": (C.c_int, [_vp, C.c_int, C.c_int]),
     "hgb_nbody_symmetric": (C.c_int, [_vp]),
     "hgb_nbody_set_segment": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int]),
+    "hgb_nbody_set_deal": (C.c_int, [_vp, C.c_int]),
     "hgb_nbody_describe": (C.c_int, [_vp, C.c_char_p, C.c_int]),
     "hgb_nbody_fp64_instr": (C.c_double, [_vp]),
     "hgb_nbody_sym_counters": (C.c_int, [_vp, C.POINTER(C.c_ulonglong)]),

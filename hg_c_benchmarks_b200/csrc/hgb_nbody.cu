@@ -32,7 +32,7 @@ struct NbShard {
     ulonglong2 *tri_ll[2] = {nullptr, nullptr};   // chain words, double-buffered by step parity, 48 B per body each
     ulonglong2 *tri_racc = nullptr;               // row accumulators between the items of a row, 48 B per body
     int2 *tri_tiles = nullptr;                    // this shard's tiles in ticket order
-    int tri_ntiles = 0, tri_plan_seg = 0, tri_plan_rows = 0, tri_plan_weight = 0;
+    int tri_ntiles = 0, tri_plan_seg = 0, tri_plan_rows = 0, tri_plan_weight = 0, tri_plan_deal = 0;
 };
 }  // namespace
 
@@ -50,6 +50,7 @@ struct hgb_nbody {
     int tri_seg = 0;        // second-generation kernel (variants 2000+): sources per segment,
     int tri_rows = 0;       // ... rows per tile,
     int tri_weight = 0;     // ... weight of the segment index in the ticket order (0 = defaults)
+    int tri_deal = 0;       // ... rows per turn of a GPU (0 = default)
     unsigned tri_step = 0;  // steps run with it so far (epoch and buffer parity)
     int tri_status = 0;     // abort flag read back after the last advance
     // chain-word buffers and control words of every shard as THIS process addresses them (own allocations,
@@ -196,8 +197,26 @@ constexpr int kTriDefaultSeg = 16384;     // sources per item
 // rows per tile (rows of a tile start together and then stagger themselves; a tile-row is the unit dealt over
 // GPUs) and weight of the segment index in the ticket order (key = tile-row + weight * segment): one GPU /
 // several (profiles/r2e_tri_sweep.txt, r2j_tri_multi_rows_weight_g8_g4.txt)
-static int tri_default_rows(const hgb_nbody *h) { return h->world > 1 ? 16 : 8; }
-static int tri_default_weight(const hgb_nbody *h) { return h->world > 1 ? 64 : 32; }
+// cooperative rows (nbody_crow_kernel, 4x fewer workers): rows handed out ONE at a time -- rows of a tile take
+// consecutive tickets and then follow each other at the minimum distance, where every small delay of the row
+// above costs a full L2 round trip (profiles/r3i_crow_schedule_*.txt: 1537 vs 1618 ms at N = 2^20)
+static int tri_default_rows(const hgb_nbody *h, int v) { return crow_variant(v) ? (h->world > 1 ? 8 : 1) : h->world > 1 ? 16 : 8; }
+static int tri_default_weight(const hgb_nbody *h, int v) { return crow_variant(v) ? (h->world > 1 ? 32 : 128) : h->world > 1 ? 64 : 32; }
+// rows per turn of a GPU (a multiple of the rows per tile): chain words cross NVLink once per turn.  Across GPUs the
+// single-row hand-out does NOT carry over (8 GPUs, N = 2^20: 1122 ms with rows 1 / weight 128 against 220 ms with
+// rows 8 / weight 32 / turns of 8, profiles/r3k_multi_g8.txt): a GPU then holds only every 8th turn of rows and the
+// ticket order of one GPU no longer follows the anti-diagonal the others are on.
+static int tri_default_deal(const hgb_nbody *h, int v) { return h->world > 1 ? (crow_variant(v) ? 8 : 16) : 1; }
+struct TriPlanParams { int seg, tr, weight, deal; };
+static TriPlanParams tri_params(const hgb_nbody *h, int v) {
+    TriPlanParams p;
+    p.seg = h->tri_seg > 0 ? h->tri_seg : kTriDefaultSeg;
+    p.tr = h->tri_rows > 0 ? h->tri_rows : tri_default_rows(h, v);
+    p.weight = h->tri_weight > 0 ? h->tri_weight : tri_default_weight(h, v);
+    p.deal = h->tri_deal > 0 ? h->tri_deal : std::max(p.tr, tri_default_deal(h, v));
+    p.deal = std::max(p.tr, p.deal / p.tr * p.tr);   // a tile never straddles two GPUs
+    return p;
+}
 constexpr long long kTriSpinLimit = 10000000000ll;   // ~5 s of SM clock: a poll that long means a lost hand-off
 
 // Tiles (b, k): the `tr` rows of tile-row b against segment k, for every segment some row of b reaches.
@@ -206,14 +225,14 @@ constexpr long long kTriSpinLimit = 10000000000ll;   // ~5 s of SM clock: a poll
 // three predecessors have a smaller key, so the order is a linear extension of the dependencies for any
 // weight >= 1; the weight spaces the segments of one row far enough apart in the ticket stream that item
 // (I, k-1) is finished when (I, k) is handed out.  Tile-row b lives on shard b mod world.
-static int tri_plan(hgb_nbody *h, NbShard &s) {
-    const int seg = h->tri_seg > 0 ? h->tri_seg : kTriDefaultSeg;
-    const int tr = h->tri_rows > 0 ? h->tri_rows : tri_default_rows(h);
-    const int weight = h->tri_weight > 0 ? h->tri_weight : tri_default_weight(h);
-    if (s.tri_tiles && s.tri_plan_seg == seg && s.tri_plan_rows == tr && s.tri_plan_weight == weight) return HGB_OK;
+static int tri_plan(hgb_nbody *h, NbShard &s, int variant) {
+    const TriPlanParams pp = tri_params(h, variant);
+    const int seg = pp.seg, tr = pp.tr, weight = pp.weight, deal = pp.deal;
+    if (s.tri_tiles && s.tri_plan_seg == seg && s.tri_plan_rows == tr && s.tri_plan_weight == weight && s.tri_plan_deal == deal) return HGB_OK;
     const int T = (h->n + 31) / 32, TB = (T + tr - 1) / tr;
     std::vector<std::pair<long long, int2>> keyed;
-    for (int b = s.index; b < TB; b += h->world) {
+    for (int b = 0; b < TB; ++b) {
+        if (((long long)b * tr / deal) % h->world != s.index) continue;   // rows I with I / deal = index (mod GPUs)
         const long long last_row = std::min(T - 1, b * tr + tr - 1);
         const int kmax = (int)(32 * last_row / seg);
         for (int k = 0; k <= kmax; ++k) keyed.push_back({((long long)b + (long long)weight * k) * 4096 + k, make_int2(b, k)});
@@ -227,7 +246,7 @@ static int tri_plan(hgb_nbody *h, NbShard &s) {
     HGB_CUDA(cudaMemcpyAsync(s.tri_tiles, tiles.data(), sizeof(int2) * tiles.size(), cudaMemcpyHostToDevice, s.dev->stream));
     HGB_CUDA(cudaStreamSynchronize(s.dev->stream));   // `tiles` goes out of scope
     s.tri_ntiles = (int)tiles.size();
-    s.tri_plan_seg = seg; s.tri_plan_rows = tr; s.tri_plan_weight = weight;
+    s.tri_plan_seg = seg; s.tri_plan_rows = tr; s.tri_plan_weight = weight; s.tri_plan_deal = deal;
     return HGB_OK;
 }
 
@@ -245,7 +264,6 @@ static int tri_alloc(hgb_nbody *h) {
             HGB_CUDA(cudaMalloc(&s.tri_racc, words));
             HGB_CUDA(cudaMemsetAsync(s.tri_racc, 0, words, s.dev->stream));
         }
-        HGB_TRY(tri_plan(h, s));
     }
     // peers store into these buffers: they must be zeroed before anybody's first step
     for (NbShard &s : h->sh) HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
@@ -395,7 +413,7 @@ static int launch_tri_step(hgb_nbody *h, int variant, int cur, int nxt) {
     const unsigned step = h->tri_step++;
     const int parity = step & 1;
     const unsigned epoch_tag = (step % 2047 + 1) << 21;
-    const int seg = h->sh[0].tri_plan_seg, rows = h->sh[0].tri_plan_rows, T = (h->n + 31) / 32;
+    const int seg = h->sh[0].tri_plan_seg, rows = h->sh[0].tri_plan_rows, deal = h->sh[0].tri_plan_deal, T = (h->n + 31) / 32;
     const int ctas = variant % 10;
     const bool prof = (variant / 10) % 10 == 1 || (variant / 10) % 10 == 3;
     for (NbShard &s : h->sh) {
@@ -425,7 +443,7 @@ static int launch_tri_step(hgb_nbody *h, int variant, int cur, int nxt) {
         HGB_CUDA(cudaSetDevice(s.dev->device));
         TriArgs a;
         memset(&a, 0, sizeof a);
-        a.src = s.state[cur]; a.npad = h->npad; a.n = h->n; a.T = T; a.seg = seg; a.tr = rows;
+        a.src = s.state[cur]; a.npad = h->npad; a.n = h->n; a.T = T; a.seg = seg; a.tr = rows; a.deal = deal;
         a.tiles = s.tri_tiles; a.ntiles = s.tri_ntiles;
         a.ll = s.tri_ll[parity];
         a.ll_down = h->tri_peer_ll[parity][(s.index + 1) % h->world];   // tile-row b+1 lives on the next shard
@@ -475,7 +493,7 @@ static int launch_tri_step(hgb_nbody *h, int variant, int cur, int nxt) {
         // kernel that shares the device (virtual shards)
         const int fgrid = std::min((h->n + 255) / 256, std::max(1, s.dev->sms / tri_shards_on_device(h, s)));
         // the finished sums are the words of the LAST row, in the buffer of the shard that ran it
-        const ulonglong2 *final_words = h->tri_peer_ll[parity][((T - 1) / rows) % h->world];
+        const ulonglong2 *final_words = h->tri_peer_ll[parity][((T - 1) / deal) % h->world];
         nbody_tri_finish_kernel<<<fgrid, 256, 0, s.dev->stream>>>(final_words, h->npad, h->n,
                                                                  epoch_tag | (unsigned)T, s.state[nxt], s.tri_ctl,
                                                                  kTriSpinLimit);
@@ -583,17 +601,24 @@ int hgb_nbody_set_segment(hgb_nbody *h, int seg, int rows_per_tile, int order_we
     return HGB_OK;
 }
 
+int hgb_nbody_set_deal(hgb_nbody *h, int rows_per_turn) {
+    HGB_ARG(h, "handle");
+    HGB_ARG(rows_per_turn >= 0 && rows_per_turn <= 65536, "rows per turn of a GPU");
+    h->tri_deal = rows_per_turn;
+    return HGB_OK;
+}
+
 int hgb_nbody_describe(const hgb_nbody *h, char *buf, int capacity) {
     HGB_ARG(h && buf && capacity > 0, "handle / buffer");
     char kern[160];
     const bool fast = h->mode == HGB_NBODY_FAST;
     const int v = sym_variant_in_effect(h);
     if (crow_variant(v)) {
-        snprintf(kern, sizeof kern, "nbody_crow_kernel<%d,%d%s> seg=%d rows=%d weight=%d", v / 100 % 10 ? 8 : 4, v % 10, (v / 10) % 10 >= 2 ? ",rowpipe" : "", h->tri_seg > 0 ? h->tri_seg : kTriDefaultSeg,
-                 h->tri_rows > 0 ? h->tri_rows : tri_default_rows(h), h->tri_weight > 0 ? h->tri_weight : tri_default_weight(h));
+        snprintf(kern, sizeof kern, "nbody_crow_kernel<%d,%d%s> seg=%d rows=%d weight=%d", v / 100 % 10 ? 8 : 4, v % 10, (v / 10) % 10 >= 2 ? ",rowpipe" : "", tri_params(h, v).seg,
+                 tri_params(h, v).tr, tri_params(h, v).weight);
     } else if (tri_variant(v)) {
-        snprintf(kern, sizeof kern, "nbody_tri_kernel<%d%s> seg=%d rows=%d weight=%d", v % 10, (v / 10) % 10 == 2 ? ",rowpipe" : "", h->tri_seg > 0 ? h->tri_seg : kTriDefaultSeg,
-                 h->tri_rows > 0 ? h->tri_rows : tri_default_rows(h), h->tri_weight > 0 ? h->tri_weight : tri_default_weight(h));
+        snprintf(kern, sizeof kern, "nbody_tri_kernel<%d%s> seg=%d rows=%d weight=%d", v % 10, (v / 10) % 10 == 2 ? ",rowpipe" : "", tri_params(h, v).seg,
+                 tri_params(h, v).tr, tri_params(h, v).weight);
     } else if (v) {
         snprintf(kern, sizeof kern, "nbody_sym_kernel<%d,%d,%d>", v / 100, v / 10 % 10, v % 10);
     } else {
@@ -793,7 +818,8 @@ static int nb_advance(hgb_nbody *h, int iterations, float *ms, bool dyn) {
     }
     if (!dyn && tri_variant(sym_variant_in_effect(h))) {
         HGB_TRY(tri_connect(h));   // first use: buffers, peer tables (collective over the ranks); may turn the variant off
-        for (NbShard &s : h->sh) HGB_TRY(tri_plan(h, s));
+        const int v = sym_variant_in_effect(h);
+        if (tri_variant(v)) for (NbShard &s : h->sh) HGB_TRY(tri_plan(h, s, v));
     }
     const int variant = dyn ? 0 : sym_variant_in_effect(h);
     const bool tri = tri_variant(variant);

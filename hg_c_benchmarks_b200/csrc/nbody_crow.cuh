@@ -129,7 +129,7 @@ nbody_crow_kernel(const __grid_constant__ TriArgs a) {
         const bool final_row = I == a.T - 1;
         const unsigned want_tag = a.epoch_tag | (unsigned)I;          // written by row I-1
         const unsigned my_tag = a.epoch_tag | (unsigned)(I + 1);
-        ulonglong2 *pub = (r == a.tr - 1 && !final_row) ? a.ll_down : a.ll;
+        ulonglong2 *pub = (I % a.deal == a.deal - 1 && !final_row) ? a.ll_down : a.ll;
         const int M = (j_end - j_begin) >> 3;             // minitiles of the item (a multiple of 4)
         const int C = M > q ? (M - q + W - 1) / W : 0;    // ... of which this warp runs m = q + W i, i < C
 

@@ -54,7 +54,8 @@ struct TriArgs {
     const double *src;        // SoA positions, component stride npad, zero beyond n
     int npad, n;
     int T;                    // rows = ceil(n / 32)
-    int seg, tr;              // sources per segment (multiple of 32), rows per tile = seg / 32
+    int seg, tr;              // sources per segment (multiple of 32), rows per tile (handed out as consecutive tickets)
+    int deal;                 // rows per turn of a GPU (a multiple of tr): rows I with I / deal = t (mod GPUs) run on GPU t
     const int2 *tiles;        // this GPU's tiles (b, k) in ticket order
     int ntiles;
     ulonglong2 *ll;           // chain words this GPU reads: [chunk of 32 sources][x, y, z][32] x 16 B
@@ -312,7 +313,7 @@ nbody_tri_kernel(const __grid_constant__ TriArgs a) {
         const unsigned want_tag = a.epoch_tag | (unsigned)I;          // written by row I-1
         const unsigned my_tag = a.epoch_tag | (unsigned)(I + 1);
         // row I+1 is the next tile-row's first row; the last row of the step keeps its words (the finished sums) here
-        ulonglong2 *pub = (r == a.tr - 1 && !final_row) ? a.ll_down : a.ll;
+        ulonglong2 *pub = (I % a.deal == a.deal - 1 && !final_row) ? a.ll_down : a.ll;
 
         const double px = sx[i0 + lane], py = sy[i0 + lane], pz = sz[i0 + lane];
         double ax = 0.0, ay = 0.0, az = 0.0;

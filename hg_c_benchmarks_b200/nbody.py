@@ -76,6 +76,11 @@ class NBody:
         check(lib().hgb_nbody_set_segment(self._h, int(seg), int(rows), int(weight)))
         return self
 
+    def deal(self, rows_per_turn=0):
+        """rows of targets per turn of a GPU when the wavefront is dealt over several GPUs (0 = default)"""
+        check(lib().hgb_nbody_set_deal(self._h, int(rows_per_turn)))
+        return self
+
     def describe(self):
         """(kernel, parallelism) the next step() will use on this handle as configured now"""
         buf = C.create_string_buffer(512)

@@ -106,6 +106,10 @@ int hgb_nbody_set_symmetric(hgb_nbody *h, int variant, int min_n);
  * handles with HGB_EXCHANGE_P2P: tile-rows of targets are dealt over the GPUs, the chain words cross NVLink
  * as tagged stores, the last row broadcasts the finished sums (no position exchange). */
 int hgb_nbody_set_segment(hgb_nbody *h, int seg, int rows_per_tile, int order_weight);
+/* Rows of targets per turn of a GPU when the pair-symmetric wavefront is dealt over several GPUs (rounded to a
+ * multiple of rows_per_tile; 0 = default 16): rows I with I / rows_per_turn = t (mod GPUs) run on GPU t, so the
+ * chain words (reference src/nbody/nbody-run.c:19-21: the running sums of accel()) cross NVLink once per turn. */
+int hgb_nbody_set_deal(hgb_nbody *h, int rows_per_turn);
 /* the variant hgb_nbody_step will use on this handle as configured now (0: the standard kernel) */
 int hgb_nbody_symmetric(const hgb_nbody *h);
 /* "<kernel> | <how targets/pairs are spread over the GPUs>" of the next hgb_nbody_step on this handle

@@ -21,8 +21,8 @@ PITCH = 34
 
 
 class CrowModel(TriModel):
-    def __init__(self, pos, seg=64, world=1, rows=2, weight=3, warps=4):
-        super().__init__(pos, seg, world, rows, weight)
+    def __init__(self, pos, seg=64, world=1, rows=2, weight=3, warps=4, deal=None):
+        super().__init__(pos, seg, world, rows, weight, deal)
         assert warps % 4 == 0
         self.W = warps
         self.npad = self.T * 32
@@ -45,7 +45,7 @@ class CrowModel(TriModel):
         want_tag, my_tag = I, I + 1
         if final_row:
             pubs = [self.llw[g] for g in range(self.world)]    # model shortcut for the finish kernel's peer reads
-        elif r == self.tr - 1:
+        elif I % self.deal == self.deal - 1:
             pubs = [self.llw[(dev + 1) % self.world]]
         else:
             pubs = [ll]

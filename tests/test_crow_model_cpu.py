@@ -29,3 +29,16 @@ def test_schedule_reproduces_the_in_order_sum(n, seg, world, rows, weight, warps
     m = CrowModel([tuple(map(float, p)) for p in pos], seg, world, rows, weight, warps)
     got = np.array(m.step(), dtype=np.float64).reshape(n, 3)
     assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("n,seg,world,rows,weight,warps,deal", [(450, 64, 2, 1, 4, 4, 4), (600, 96, 3, 2, 7, 4, 6), (700, 128, 4, 1, 16, 4, 3),
+                                                                (500, 64, 2, 2, 3, 4, 5), (333, 32, 8, 1, 2, 8, 2)])
+def test_rows_handed_out_singly_but_dealt_to_gpus_in_turns(n, seg, world, rows, weight, warps, deal):
+    """rows per tile (consecutive tickets) and rows per turn of a GPU are separate knobs"""
+    from oracle import port
+    pos = synth.uniform_cube(n, seed=n + 1)
+    want = np.zeros_like(pos)
+    port.nbody_step_range(pos, want, 0, n)
+    m = CrowModel([tuple(map(float, p)) for p in pos], seg, world, rows, weight, warps, deal)
+    got = np.array(m.step(), dtype=np.float64).reshape(n, 3)
+    assert np.array_equal(got, want)

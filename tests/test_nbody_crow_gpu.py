@@ -20,10 +20,10 @@ def sha(a):
     return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
 
 
-def crow_step(hgb, pos, iters, variant=3002, seg=0, ngpus=1, want_prev=False, rows=0, weight=0):
+def crow_step(hgb, pos, iters, variant=3002, seg=0, ngpus=1, want_prev=False, rows=0, weight=0, deal=0):
     kind = hgb.EXCHANGE_P2P if ngpus > 1 else hgb.EXCHANGE_NCCL
     with hgb.nbody.NBody(pos.shape[0], ngpus=ngpus, exchange=kind) as nb:
-        nb.symmetric(variant, 0).segment(seg, rows, weight).upload(pos)
+        nb.symmetric(variant, 0).segment(seg, rows, weight).deal(deal).upload(pos)
         assert hgb.lib().hgb_nbody_symmetric(nb._h) == variant
         assert nb.describe()[0].startswith("nbody_crow_kernel")
         nb.step(iters)
@@ -136,6 +136,11 @@ def test_crow_rows_dealt_over_gpus_are_bit_identical(hgb, monkeypatch, n, iters,
         for rows in (0, 1, 5):
             cur, prev = crow_step(hgb, pos, iters, seg=seg, ngpus=g, want_prev=True, rows=rows, weight=rows)
             assert np.array_equal(cur, one_cur) and np.array_equal(prev, one_prev), (g, rows)
+        for variant, rows, deal in ((3002, 1, 4), (3002, 2, 6), (2002, 1, 3)):   # rows handed out singly, dealt to the GPUs in turns
+            cur, prev = crow_step(hgb, pos, iters, variant, seg=seg, ngpus=g, want_prev=True, rows=rows, weight=8, deal=deal) \
+                if variant == 3002 else (None, None)
+            if variant == 3002:
+                assert np.array_equal(cur, one_cur) and np.array_equal(prev, one_prev), (g, rows, deal)
 
 
 def test_crow_64k_plummer_all_bodies_equal_the_standard_kernel(hgb):

@@ -17,8 +17,9 @@ MT = 8
 
 
 class TriModel:
-    def __init__(self, pos, seg=64, world=1, rows=2, weight=3):
+    def __init__(self, pos, seg=64, world=1, rows=2, weight=3, deal=None):
         assert seg % 32 == 0 and rows >= 1 and weight >= 1
+        self.deal = rows if deal is None else max(rows, deal // rows * rows)   # rows per turn of a GPU, a multiple of the rows per tile
         self.pos, self.n, self.seg, self.world, self.weight = pos, len(pos), seg, world, weight
         self.T = (self.n + 31) // 32
         self.tr = rows                                    # rows per tile
@@ -35,7 +36,9 @@ class TriModel:
     def plan(self, index):
         """tiles of shard `index` in ticket order (hgb_nbody.cu tri_plan): key b + weight * k, then k"""
         tiles = []
-        for b in range(index, self.TS, self.world):
+        for b in range(self.TS):
+            if (b * self.tr // self.deal) % self.world != index:
+                continue
             last_row = min(self.T - 1, b * self.tr + self.tr - 1)
             for k in range(32 * last_row // self.seg + 1):
                 tiles.append(((b + self.weight * k) * 4096 + k, b, k))
@@ -56,7 +59,7 @@ class TriModel:
         final_row = I == self.T - 1
         want_tag, my_tag = I, I + 1
         # where row I+1 reads: same GPU, or the next super-row's GPU after the last row of a super-row
-        pub = [(dev + 1) % self.world] if r == self.tr - 1 else [dev]
+        pub = [(dev + 1) % self.world] if I % self.deal == self.deal - 1 else [dev]
         if final_row:
             pub = list(range(self.world))
         if k > 0:
@@ -107,7 +110,7 @@ class TriModel:
         order = sorted((((b + self.weight * k) * 4096 + k, b, k, g) for g in range(self.world) for (b, k) in plans[g]))
         seen = set()
         for _, b, k, g in order:
-            assert b % self.world == g and (b, k) not in seen
+            assert (b * self.tr // self.deal) % self.world == g and (b, k) not in seen
             seen.add((b, k))
             for r in range(self.tr):
                 self.item(g, b, k, r)

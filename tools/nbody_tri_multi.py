@@ -17,11 +17,11 @@ gs = [int(a) for a in sys.argv[2:]] or [g for g in (1, 2, 4, 8) if g <= torch.cu
 pos = synth.uniform_cube(n, seed=1)
 
 
-def run(g, variant, seg=0, rows=0, weight=0, steps=2):
+def run(g, variant, seg=0, rows=0, weight=0, steps=2, deal=0):
     with H.nbody.NBody(n, ngpus=g, exchange=H._abi.EXCHANGE_P2P if variant else H._abi.EXCHANGE_NCCL) as nb:
         nb.symmetric(variant, 0)
         if variant >= 2000:
-            nb.segment(seg, rows, weight)
+            nb.segment(seg, rows, weight).deal(deal)
         nb.upload(pos)
         nb.step(1)
         nb.upload(pos)
@@ -51,13 +51,16 @@ for g in gs:
     if os.environ.get("TRI_GRID") == "small":
         grid = [(2002, 16384, 8, 32), (2002, 16384, 16, 32), (2002, 16384, 16, 64), (2002, 8192, 16, 32), (2003, 16384, 16, 32)]
     if os.environ.get("TRI_GRID") == "crow":
-        grid = [(2002, 16384, 16, 64), (3002, 16384, 8, 32), (3002, 16384, 16, 64), (3002, 16384, 4, 16), (3002, 8192, 8, 32),
-                (3002, 16384, 8, 64), (3002, 32768, 8, 32)]
-    for variant, seg, rows, weight in grid:
-        ms, out, _, what = run(g, variant, seg, rows, weight)
-        print(f"g={g} n={n} tri {variant} seg={seg:6d} rows={rows:3d} weight={weight:3d}: {ms:9.3f} ms  "
+        grid = [(3002, 0, 0, 0, 0), (3002, 16384, 8, 32, 16), (3002, 16384, 4, 64, 8), (3002, 16384, 8, 16, 8), (3002, 16384, 8, 64, 8),
+                (3002, 16384, 4, 32, 4), (3002, 8192, 8, 64, 8), (3002, 32768, 8, 32, 8), (3002, 16384, 4, 32, 8)]
+    for spec in grid:
+        variant, seg, rows, weight = spec[:4]
+        deal = spec[4] if len(spec) > 4 else 0
+        ms, out, _, what = run(g, variant, seg, rows, weight, deal=deal)
+        print(f"g={g} n={n} {'crow' if variant >= 3000 else 'tri'} {variant} seg={seg:6d} rows={rows:3d} weight={weight:3d} deal={deal:3d}: {ms:9.3f} ms  "
               f"{n * n / (ms * 1e-3):.4e} inter/s  same={np.array_equal(out, ref)}  [{what[0]}]", flush=True)
-    ms, out, c, _ = run(g, 3012 if os.environ.get("TRI_GRID") == "crow" else 2012, 16384, 16 if os.environ.get("TRI_GRID") != "crow" else 8, 64 if os.environ.get("TRI_GRID") != "crow" else 32, steps=1)
+    crow = os.environ.get("TRI_GRID") == "crow"
+    ms, out, c, _ = run(g, 3012 if crow else 2012, 16384, 8 if crow else 16, 32 if crow else 64, steps=1, deal=8 if crow else 16)
     tot = max(1, c[2])
     print(f"g={g} n={n} tri 2012 (profiling, shard 0): {ms:9.3f} ms; chain-word waits {100.0 * c[0] / tot:.1f} %, "
           f"row-accumulator waits {100.0 * c[1] / tot:.1f} %, items {c[4]}, cycles per item {tot / max(1, c[4]):.0f}", flush=True)
