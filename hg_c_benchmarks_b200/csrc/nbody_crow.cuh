@@ -235,8 +235,8 @@ nbody_crow_kernel(const __grid_constant__ TriArgs a) {
                 double vx[8], vy[8], vz[8];
                 forces_and_column<ALLV>(px, py, pz, xj, yj, zj, vx, vy, vz, key, col_prev, chain, cnt, lane < 24);
                 if (more) fetch_sources(i + 1);
+                publish(const_cast<ulonglong2 *>(at) + to_pub, chain);   // before the row pass: the next row gets it that much earlier
                 row_pass(i, mine, vx, vy, vz);
-                publish(const_cast<ulonglong2 *>(at) + to_pub, chain);
                 __syncwarp();   // column lanes read these values during the next minitile; ring slot hand-over
             };
             if constexpr (ROWPIPE) {
