@@ -146,7 +146,9 @@ template <int R, int U, int CTAS, bool PROF = false>
 static int launch_sym_variant(cudaStream_t st, int sms, const double *src, int npad, int n, ulonglong2 *ll,
                               unsigned epoch_tag, int *ctl) {
     const size_t smem = (size_t)kSymWarps * 6 * 3 * 32 * sizeof(double);   // per warp: 6 arrays x 3 chunks of 32 (18 KB per CTA)
-    nbody_sym_kernel<R, U, CTAS, PROF><<<sms * CTAS, kSymWarps * 32, smem, st>>>(src, npad, n, ll, epoch_tag, ctl);
+    static const int hyst = getenv("HGB_NBODY_SYM_HYST") ? atoi(getenv("HGB_NBODY_SYM_HYST")) : 0;
+    const char *h_now = getenv("HGB_NBODY_SYM_HYST_NOW");   // experiments: re-read at every launch
+    nbody_sym_kernel<R, U, CTAS, PROF><<<sms * CTAS, kSymWarps * 32, smem, st>>>(src, npad, n, ll, epoch_tag, ctl, h_now ? atoi(h_now) : hyst);
     HGB_LAUNCHED();
     return HGB_OK;
 }
@@ -654,6 +656,18 @@ int hgb_nbody_sym_counters(hgb_nbody *h, unsigned long long *out7) {
     HGB_CUDA(cudaSetDevice(s.dev->device));
     HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
     HGB_CUDA(cudaMemcpy(out7, ctl + 8, 7 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    if (getenv("HGB_NBODY_SYM_HIST") && ctl == s.sym_ctl) {   // diagnostic: wait cycles by eighth of the row x quarter of the workers
+        unsigned long long hist[40];
+        HGB_CUDA(cudaMemcpy(hist, ctl + 24, sizeof hist, cudaMemcpyDeviceToHost));
+        fprintf(stderr, "sym: chunks the predecessor is ahead at a chunk open (0, 1, 2, 3, 4-7, 8-15, 16-31, 32+):");
+        for (int e = 0; e < 8; ++e) fprintf(stderr, " %llu", hist[32 + e]);
+        fprintf(stderr, "\n");
+        for (int q = 0; q < 4; ++q) {
+            fprintf(stderr, "sym wait cycles, workers in quarter %d, by eighth of the row:", q);
+            for (int e = 0; e < 8; ++e) fprintf(stderr, " %.3e", (double)hist[q * 8 + e]);
+            fprintf(stderr, "\n");
+        }
+    }
     return HGB_OK;
 }
 

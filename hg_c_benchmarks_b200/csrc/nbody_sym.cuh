@@ -40,7 +40,7 @@
 
 namespace hgb {
 
-constexpr int kSymCtlInts = 32;   // ctl[0] = ticket counter, ctl[1] = range flag, ctl[8..] profiling counters
+constexpr int kSymCtlInts = 128;   // ctl[0] = ticket counter, ctl[1] = range flag, ctl[8..21] profiling counters, ctl[24..] (PROF) wait cycles by position in the row x worker size class
 
 // Hand-off words (the "LL" scheme of collective libraries): every 64-bit word carries 32 bits of
 // payload and a 32-bit tag, so a naturally aligned 8-byte store publishes data and flag together --
@@ -134,7 +134,7 @@ constexpr int kSymWarps = 4;   // warps (independent workers) per CTA
 // predicate-free loop, predicated steps, whole workers) into ctl[8..] -- a diagnostic instantiation.
 template <int R, int U, int CTAS, bool PROF = false>
 __global__ void __launch_bounds__(kSymWarps * 32, CTAS)
-nbody_sym_kernel(const double *__restrict__ src, int npad, int n, ulonglong2 *ll, unsigned epoch_tag, int *ctl) {
+nbody_sym_kernel(const double *__restrict__ src, int npad, int n, ulonglong2 *ll, unsigned epoch_tag, int *ctl, int hyst) {
     constexpr int BS = 32 * R, CH = 32, RING = 3 * CH;   // block of targets, hand-off chunk, ring entries
     constexpr unsigned FULL = 0xffffffffu;
     static_assert(CH % U == 0, "groups of U steps must not straddle a chunk boundary");
@@ -164,6 +164,7 @@ nbody_sym_kernel(const double *__restrict__ src, int npad, int n, ulonglong2 *ll
             valid[r] = tgt0 + r < n;
         }
         int e = (RING - lane) % RING;   // ring entry of source j = s - lane
+        const int last_chunk_of_row = (jend - 1) / CH;
 
         // Prefetch registers: one entry (this lane's) of the chunk that will be opened next -- the
         // source position and, for a lower chunk, the tagged chain-accumulator words.  The loads are
@@ -192,16 +193,43 @@ nbody_sym_kernel(const double *__restrict__ src, int npad, int n, ulonglong2 *ll
             if (lower) {
                 const ulonglong2 *q = ll + (size_t)c * 3 * CH + lane;
                 // every lane polls its own three entries; the warp leaves together
-                while (!__all_sync(FULL, ll_ok(pf_ax, want_tag) && ll_ok(pf_ay, want_tag) && ll_ok(pf_az, want_tag))) {
-                    __nanosleep(20);
-                    pf_ax = ll_load(q); pf_ay = ll_load(q + CH); pf_az = ll_load(q + 2 * CH);
+                if (!__all_sync(FULL, ll_ok(pf_ax, want_tag) && ll_ok(pf_ay, want_tag) && ll_ok(pf_az, want_tag))) {
+                    // This worker has caught up with the one before it.  hyst > 0: let it fall `hyst` chunks behind
+                    // (wait for a later chunk of the predecessor's stream first), so that the next prefetches find
+                    // their words instead of paying a round trip at every chunk.
+                    const int ahead = min(c + hyst, (w - 1) * R - 1);
+                    if (hyst > 0 && ahead > c) {
+                        const ulonglong2 *qa = ll + (size_t)ahead * 3 * CH + lane;
+                        while (!__all_sync(FULL, ll_ok(ll_load(qa + 2 * CH), want_tag))) __nanosleep(100);
+                    }
+                    do {
+                        pf_ax = ll_load(q); pf_ay = ll_load(q + CH); pf_az = ll_load(q + 2 * CH);
+                        if (__all_sync(FULL, ll_ok(pf_ax, want_tag) && ll_ok(pf_ay, want_tag) && ll_ok(pf_az, want_tag))) break;
+                        __nanosleep(20);
+                    } while (true);
                 }
             }
             const long long a1 = now();
             rx[slot] = pf_x; ry[slot] = pf_y; rz[slot] = pf_z;
             if (lower) { rax[slot] = ll_unpack(pf_ax); ray[slot] = ll_unpack(pf_ay); raz[slot] = ll_unpack(pf_az); }
             __syncwarp();
-            if (PROF) { t_wait += a1 - a0; t_open += now() - a1; ++n_chunks; }
+            if (PROF) {
+                t_wait += a1 - a0; t_open += now() - a1; ++n_chunks;
+                // where the waiting happens: tenth of the row (by chunk) x quarter of the worker range
+                if (lane == 0 && (c & 63) == 0 && c + 40 < w * R) {   // every 64th chunk: how many chunks ahead the predecessor has published (0..32+)
+                    int ahead = 0;
+                    for (int k = 1; k <= 32; ++k) {
+                        const ulonglong2 t = ll_load(ll + (size_t)(c + k) * 3 * CH);
+                        if ((unsigned)(t.x >> 32) != want_tag) break;
+                        ahead = k;
+                    }
+                    atomicAdd(reinterpret_cast<unsigned long long *>(ctl + 24) + 32 + min(7, ahead >= 32 ? 7 : ahead >= 16 ? 6 : ahead >= 8 ? 5 : ahead >= 4 ? 4 : ahead), 1ull);
+                }
+                if (lane == 0 && a1 - a0 > 0) {
+                    const int tenth = min(9, 10 * c / (last_chunk_of_row + 1)), quarter = min(3, 4 * w / T);
+                    atomicAdd(reinterpret_cast<unsigned long long *>(ctl + 24) + (quarter * 8 + min(7, tenth * 8 / 10)), (unsigned long long)(a1 - a0));
+                }
+            }
         };
         // every lane is through with chunk c: publish its chain accumulators for worker w+1
         auto close_chunk = [&](int c) {
@@ -247,20 +275,19 @@ nbody_sym_kernel(const double *__restrict__ src, int npad, int n, ulonglong2 *ll
                 if (have_u) { ux = rax[es[u]]; uy = ray[es[u]]; uz = raz[es[u]]; }
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
+                    // branch-free (selects): the diagonal is the serial tail of every worker, and divergent branches
+                    // around single DADDs made an edge group cost twice a predicate-free one
                     const int i = tgt0 + r;
-                    if (act && i < n) {
-                        if (j == i) {          // lower sum of target i is complete: it becomes j's chain
-                            ux = ax[r]; uy = ay[r]; uz = az[r];
-                            have_u = true;
-                        } else if (j < i) {
-                            ax[r] = __dadd_rn(ax[r], vx[u * R + r]);
-                            ay[r] = __dadd_rn(ay[r], vy[u * R + r]);
-                            az[r] = __dadd_rn(az[r], vz[u * R + r]);
-                            ux = __dsub_rn(ux, vx[u * R + r]);
-                            uy = __dsub_rn(uy, vy[u * R + r]);
-                            uz = __dsub_rn(uz, vz[u * R + r]);
-                        }
-                    }
+                    const bool ok = act && i < n;
+                    const bool eq = ok && j == i;      // lower sum of target i is complete: it becomes j's chain
+                    const bool lt = ok && j < i;
+                    const double nax = __dadd_rn(ax[r], vx[u * R + r]), nay = __dadd_rn(ay[r], vy[u * R + r]),
+                                 naz = __dadd_rn(az[r], vz[u * R + r]);
+                    const double nux = __dsub_rn(ux, vx[u * R + r]), nuy = __dsub_rn(uy, vy[u * R + r]),
+                                 nuz = __dsub_rn(uz, vz[u * R + r]);
+                    ux = eq ? ax[r] : (lt ? nux : ux); uy = eq ? ay[r] : (lt ? nuy : uy); uz = eq ? az[r] : (lt ? nuz : uz);
+                    ax[r] = lt ? nax : ax[r]; ay[r] = lt ? nay : ay[r]; az[r] = lt ? naz : az[r];
+                    have_u = have_u || eq;
                 }
                 if (have_u) { rax[es[u]] = ux; ray[es[u]] = uy; raz[es[u]] = uz; }
                 __syncwarp();
@@ -307,6 +334,7 @@ nbody_sym_kernel(const double *__restrict__ src, int npad, int n, ulonglong2 *ll
         const bool full = i0 + BS <= n;
 
         int s = 0;
+        bool early_closed = false;
         const int s_end = jend - 1 + 31, last_chunk = (jend - 1) / CH;
 #pragma unroll 1
         while (s <= s_end) {
@@ -315,6 +343,13 @@ nbody_sym_kernel(const double *__restrict__ src, int npad, int n, ulonglong2 *ll
                 if (c >= 2) close_chunk(c - 2);   // lane 31 left it 2 steps ago at the latest
                 open_chunk(c);
                 if (c + 1 <= last_chunk) prefetch_chunk(c + 1);
+            } else if (s == (last_chunk + 1) * CH && last_chunk >= 1 && !early_closed) {
+                // The same rule one chunk further: every lane has left chunk last_chunk-1 (the first chunk of the block
+                // itself).  Worker w+1 can stream it while this worker finishes its diagonal: the serial tail per
+                // worker (stream the predecessor's two chunks, then the own diagonal) loses one chunk time, and with a
+                // wavefront whose leaders advance 4 chunks per tail that tail -- not the FP64 pipe -- sets the pace.
+                close_chunk(last_chunk - 1);
+                early_closed = true;
             }
             const int lim = min(i0, (s / CH + 1) * CH);   // end of the predicate-free run inside this chunk
             const long long b0 = now();
@@ -333,7 +368,7 @@ nbody_sym_kernel(const double *__restrict__ src, int npad, int n, ulonglong2 *ll
                 if (PROF) t_slow += now() - b0;
             }
         }
-        if (last_chunk >= 1) close_chunk(last_chunk - 1);
+        if (last_chunk >= 1 && !early_closed) close_chunk(last_chunk - 1);
         close_chunk(last_chunk);   // the block's own chunks, tagged w+1, let worker w+1 in
         if (PROF) t_work += now() - w_begin;
     }

@@ -11,12 +11,14 @@ import hg_c_benchmarks_b200 as H  # noqa: E402
 from hg_c_benchmarks_b200 import synth  # noqa: E402
 
 W = 16384
-for k in (3, 7):
+FINE = {3: (36, 40, 44, 48, 52, 56, 60), 5: (48, 64, 80, 96, 128), 7: (52, 56, 60, 64, 69, 74, 80, 86, 93, 103, 128, 147)}
+fine = "fine" in sys.argv
+for k in ((3, 5, 7) if fine else (3, 7)):
     p = k // 2
     kern = synth.kernel_dense(k)
     for rows in (16384, 2048):
         img = synth.add_padding(synth.image_float(W, rows, seed=3), p)
-        for chunk in ((0,) if rows == 16384 else (0, 16, 24, 32, 48, 64, 96, 114, 128, 171, 228, 256, 342, 512)):
+        for chunk in ((0,) if rows == 16384 else ((0,) + FINE[k]) if fine else (0, 16, 24, 32, 48, 64, 96, 114, 128, 171, 228, 256, 342, 512)):
             if k == 7 and chunk and chunk < 32:
                 continue
             with H.convolution.Conv2D(W, rows, p) as cv:
