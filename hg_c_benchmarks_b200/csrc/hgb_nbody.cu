@@ -146,7 +146,9 @@ template <int R, int U, int CTAS, bool PROF = false>
 static int launch_sym_variant(cudaStream_t st, int sms, const double *src, int npad, int n, ulonglong2 *ll,
                               unsigned epoch_tag, int *ctl) {
     const size_t smem = (size_t)kSymWarps * 6 * 3 * 32 * sizeof(double);   // per warp: 6 arrays x 3 chunks of 32 (18 KB per CTA)
-    static const int hyst = getenv("HGB_NBODY_SYM_HYST") ? atoi(getenv("HGB_NBODY_SYM_HYST")) : 0;
+    // a worker that has caught up with its predecessor falls one chunk behind before it goes on: 1384-1394 ms against
+    // 1413-1420 at N = 2^20 in three runs (profiles/r3r_sym_hysteresis.txt, r3s_*); more than one chunk costs time
+    static const int hyst = getenv("HGB_NBODY_SYM_HYST") ? atoi(getenv("HGB_NBODY_SYM_HYST")) : 1;
     const char *h_now = getenv("HGB_NBODY_SYM_HYST_NOW");   // experiments: re-read at every launch
     nbody_sym_kernel<R, U, CTAS, PROF><<<sms * CTAS, kSymWarps * 32, smem, st>>>(src, npad, n, ll, epoch_tag, ctl, h_now ? atoi(h_now) : hyst);
     HGB_LAUNCHED();
