@@ -8,6 +8,7 @@
 #include "nbody_sym.cuh"
 #include "nbody_tri.cuh"
 #include "nbody_crow.cuh"
+#include "nbody_seg.cuh"
 
 using namespace hgb;
 
@@ -33,6 +34,10 @@ struct NbShard {
     ulonglong2 *tri_racc = nullptr;               // row accumulators between the items of a row, 48 B per body
     int2 *tri_tiles = nullptr;                    // this shard's tiles in ticket order
     int tri_ntiles = 0, tri_plan_seg = 0, tri_plan_rows = 0, tri_plan_weight = 0, tri_plan_deal = 0;
+    // first-generation warp on the segmented schedule (nbody_seg.cuh): row sums between items, tiles in ticket order
+    ulonglong2 *seg_racc = nullptr;
+    int2 *seg_tiles = nullptr;
+    int seg_ntiles = 0, seg_plan_seg = 0, seg_plan_rows = 0, seg_plan_weight = 0;
 };
 }  // namespace
 
@@ -133,8 +138,11 @@ static bool crow_variant(int v) {
 // 202C: row pass fused into the next minitile's force block (ROWPIPE)
 static bool tri_variant(int v) { return (v >= 2001 && v <= 2023 && (v % 10) >= 1 && (v % 10) <= 3) || crow_variant(v); }
 
+// 4242 (5242 with span counters): the first generation's systolic warp (R = 2, U = 4, 2 CTAs per SM) on the segmented schedule
+static bool seg_variant(int v) { return v == 4242 || v == 5242 || v == 6242 || v == 7242; }   // 6242 / 7242: pipelined groups
+
 static bool sym_variant_known(int v) {
-    if (tri_variant(v)) return true;
+    if (tri_variant(v) || seg_variant(v)) return true;
     switch (v) {
         case 124: case 146: case 148: case 224: case 226: case 228: case 243: case 413: case 423: case 422: case 242: case 183: case 182: case 144: case 241: case 181: case 421: case 1226: case 1242:
             return true;
@@ -512,6 +520,65 @@ static int launch_tri_step(hgb_nbody *h, int variant, int cur, int nxt) {
     return HGB_OK;
 }
 
+// ---- first-generation warp on the segmented schedule (nbody_seg.cuh): one GPU -----------------------------
+constexpr int kSegDefaultSeg = 16384, kSegDefaultRows = 2, kSegDefaultWeight = 128;
+static int seg_plan(hgb_nbody *h, NbShard &s) {
+    const int seg = h->tri_seg > 0 ? h->tri_seg : kSegDefaultSeg;
+    const int tr = h->tri_rows > 0 ? h->tri_rows : kSegDefaultRows;
+    const int weight = h->tri_weight > 0 ? h->tri_weight : kSegDefaultWeight;
+    if (s.seg_tiles && s.seg_plan_seg == seg && s.seg_plan_rows == tr && s.seg_plan_weight == weight) return HGB_OK;
+    constexpr int BS = 64;   // targets per block (R = 2)
+    const int T = (h->n + BS - 1) / BS, TB = (T + tr - 1) / tr;
+    std::vector<std::pair<long long, int2>> keyed;
+    for (int b = 0; b < TB; ++b) {
+        const long long last_row = std::min(T - 1, b * tr + tr - 1);
+        const int kmax = (int)(BS * last_row / seg);
+        for (int k = 0; k <= kmax; ++k) keyed.push_back({((long long)b + (long long)weight * k) * 4096 + k, make_int2(b, k)});
+    }
+    std::sort(keyed.begin(), keyed.end(), [](const auto &x, const auto &y) { return x.first < y.first; });
+    std::vector<int2> tiles(keyed.size());
+    for (size_t i = 0; i < keyed.size(); ++i) tiles[i] = keyed[i].second;
+    if (s.seg_tiles) cudaFree(s.seg_tiles);
+    s.seg_tiles = nullptr;
+    HGB_CUDA(cudaMalloc(&s.seg_tiles, sizeof(int2) * (tiles.size() + 1)));
+    HGB_CUDA(cudaMemcpyAsync(s.seg_tiles, tiles.data(), sizeof(int2) * tiles.size(), cudaMemcpyHostToDevice, s.dev->stream));
+    HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
+    s.seg_ntiles = (int)tiles.size();
+    s.seg_plan_seg = seg; s.seg_plan_rows = tr; s.seg_plan_weight = weight;
+    return HGB_OK;
+}
+
+static int launch_seg(hgb_nbody *h, int variant, NbShard &s, const double *src, const PeerOut &out) {
+    cudaStream_t st = s.dev->stream;
+    if (!s.sym_ctl) {
+        HGB_CUDA(cudaMalloc(&s.sym_ctl, sizeof(int) * kSymCtlInts));
+        HGB_CUDA(cudaMalloc(&s.sym_ll, 48ull * h->npad));
+        HGB_CUDA(cudaMemsetAsync(s.sym_ll, 0, 48ull * h->npad, st));   // tag 0 is never expected
+    }
+    if (!s.seg_racc) {
+        HGB_CUDA(cudaMalloc(&s.seg_racc, 48ull * h->npad));
+        HGB_CUDA(cudaMemsetAsync(s.seg_racc, 0, 48ull * h->npad, st));
+    }
+    HGB_TRY(seg_plan(h, s));
+    HGB_CUDA(cudaMemsetAsync(s.sym_ctl, 0, sizeof(int) * kSymCtlInts, st));
+    s.sym_epoch = s.sym_epoch % 2047 + 1;
+    SegArgs a;
+    memset(&a, 0, sizeof a);
+    a.src = src; a.npad = h->npad; a.n = h->n; a.T = (h->n + 63) / 64; a.seg = s.seg_plan_seg; a.tr = s.seg_plan_rows;
+    a.tiles = s.seg_tiles; a.ntiles = s.seg_ntiles; a.ll = s.sym_ll; a.racc = s.seg_racc;
+    a.epoch_tag = s.sym_epoch << 21; a.ctl = s.sym_ctl; a.spin_limit = kTriSpinLimit;
+    const size_t smem = (size_t)kSymWarps * 6 * 3 * 32 * sizeof(double);
+    const int grid = s.dev->sms * 2;
+    if (variant == 5242) nbody_seg_kernel<2, 4, 2, true><<<grid, kSymWarps * 32, smem, st>>>(a);
+    else if (variant == 6242) nbody_seg_kernel<2, 4, 2, false, true><<<grid, kSymWarps * 32, smem, st>>>(a);
+    else if (variant == 7242) nbody_seg_kernel<2, 4, 2, true, true><<<grid, kSymWarps * 32, smem, st>>>(a);
+    else nbody_seg_kernel<2, 4, 2, false><<<grid, kSymWarps * 32, smem, st>>>(a);
+    HGB_LAUNCHED();
+    nbody_sym_finish_kernel<<<(h->n + 255) / 256, 256, 0, st>>>(s.sym_ll, h->npad, h->n, out);
+    HGB_LAUNCHED();
+    return launch_step(h, s, src, 0, h->n, nullptr, out, nullptr, s.sym_ctl + 1);
+}
+
 // whole step on shard s: tickets/flags reset, wavefront kernel, G*acc, conditional redo
 static int launch_sym(const hgb_nbody *h, int variant, NbShard &s, const double *src, const PeerOut &out) {
     cudaStream_t st = s.dev->stream;
@@ -624,7 +691,11 @@ int hgb_nbody_describe(const hgb_nbody *h, char *buf, int capacity) {
         snprintf(kern, sizeof kern, "nbody_tri_kernel<%d%s> seg=%d rows=%d weight=%d", v % 10, (v / 10) % 10 == 2 ? ",rowpipe" : "", tri_params(h, v).seg,
                  tri_params(h, v).tr, tri_params(h, v).weight);
     } else if (v) {
-        snprintf(kern, sizeof kern, "nbody_sym_kernel<%d,%d,%d>", v / 100, v / 10 % 10, v % 10);
+        if (seg_variant(v))
+            snprintf(kern, sizeof kern, "nbody_seg_kernel<2,4,2%s> seg=%d rows=%d weight=%d", v >= 6000 ? ",pipelined" : "", h->tri_seg > 0 ? h->tri_seg : kSegDefaultSeg,
+                     h->tri_rows > 0 ? h->tri_rows : kSegDefaultRows, h->tri_weight > 0 ? h->tri_weight : kSegDefaultWeight);
+        else
+            snprintf(kern, sizeof kern, "nbody_sym_kernel<%d,%d,%d>", v / 100, v / 10 % 10, v % 10);
     } else {
         int block = 0, unroll = 0, warps = 0;
         const int count = h->n < h->slice ? h->n : h->slice;
@@ -711,6 +782,8 @@ int hgb_nbody_destroy(hgb_nbody *h) {
         if (s.tri_ll[1]) cudaFree(s.tri_ll[1]);
         if (s.tri_racc) cudaFree(s.tri_racc);
         if (s.tri_tiles) cudaFree(s.tri_tiles);
+        if (s.seg_racc) cudaFree(s.seg_racc);
+        if (s.seg_tiles) cudaFree(s.seg_tiles);
     }
     delete h;
     return HGB_OK;
@@ -864,6 +937,8 @@ static int nb_advance(hgb_nbody *h, int iterations, float *ms, bool dyn) {
                         s.state[cur], h->npad, h->n, t0, count, nullptr, out, nullptr, d);
                     HGB_LAUNCHED();
                 }
+            } else if (seg_variant(variant)) {   // first-generation warp, segmented schedule
+                HGB_TRY(launch_seg(h, variant, s, s.state[cur], out));
             } else if (variant) {   // first-generation wavefront (variants R*100 + U*10 + CTAs)
                 HGB_TRY(launch_sym(h, variant, s, s.state[cur], out));
             } else {
@@ -906,6 +981,17 @@ static int nb_advance(hgb_nbody *h, int iterations, float *ms, bool dyn) {
     }
     HGB_CUDA(cudaGetLastError());
     if (ms) *ms = worst;
+    if (seg_variant(variant) && iterations > 0) {
+        NbShard &s0 = h->sh[0];
+        int c[8] = {0};
+        HGB_CUDA(cudaMemcpy(c, s0.sym_ctl, sizeof c, cudaMemcpyDeviceToHost));
+        if (c[2]) {
+            set_error("segmented pair-symmetric wavefront abandoned: a hand-off did not arrive within the spin limit; %d tickets of %d items, "
+                      "wanted tag epoch %u id %d, found tag %#x, chain word %d, row-sum word %d", c[0], s0.seg_ntiles * s0.seg_plan_rows,
+                      (unsigned)c[6] >> 21, c[6] & 0x1fffff, (unsigned)c[7], c[5], c[4]);
+            return HGB_ERR_STATE;
+        }
+    }
     if (tri && iterations > 0) {   // a hand-off that never arrived: the kernels gave up instead of hanging
         for (NbShard &s : h->sh) {
             int flag = 0;
