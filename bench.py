@@ -673,7 +673,7 @@ def main():
                          "unit": "TFLOP/s",
                          "frac": per_gpu * FLOP_PER_INTERACTION / 1e12 / (clock_true_tf if clock_true_tf else tf.value),
                          "kernel": nb_kernel,
-                         "traffic": ncu_traffic("nbody_crow" if sym >= 3000 else "nbody_tri" if sym >= 2000 else "nbody_sym" if sym else "nbody_step_kernel<"),
+                         "traffic": ncu_traffic("nbody_seg" if sym >= 4000 else "nbody_crow" if sym >= 3000 else "nbody_tri" if sym >= 2000 else "nbody_sym" if sym else "nbody_step_kernel<"),
                          "traffic_note": "ncu dram bytes per launch of this kernel on ONE GPU (profiles/ncu_traffic.json; nbody_crow_kernel captured at n = 2^18, the others at 2^20); positions (24 MiB) and hand-off words live in L2",
                          "per_gpu": True,
                          "peak_source": ("clock-true FP64 rate: SMs x 64 DFMA lanes x 2 flop x the SM clock sampled by nvidia-smi during "

@@ -180,12 +180,14 @@ constexpr int kTriMinNPerGpu = 131072;
 // decides is the number of bodies per GPU: it sets how long the wavefronts' serial chains are against the work.
 //   one GPU:   n < 49 152 standard kernel | < 229 376 cooperative rows (nbody_crow_kernel: +19 % at 64k, +31 % at 96k)
 //              | < 786 432 one warp per row (nbody_tri_kernel: +33 % at 384k, 374 vs 405 ms at 512k)
-//              | else first generation (nbody_sym_kernel: 1410 vs 1474 ms at 2^20)
+//              | else the first generation's systolic warp on the segmented schedule, groups software-pipelined
+//                (nbody_seg_kernel: 1364 ms at 2^20 against 1410 for nbody_sym_kernel and 1440 for nbody_tri_kernel; 789 vs 830 at 786 432)
 //   g GPUs:    n / g < 65 536 standard kernel with ncclAllGather | < 262 144 cooperative rows | else one warp per row
 constexpr int kCrowDefaultVariant = 3002;
+constexpr int kSegDefaultVariant = 6242;
 static int auto_variant(const hgb_nbody *h) {
     const long long per = h->n / h->world;
-    if (h->world == 1) return h->n >= 786432 ? kSymDefaultVariant : h->n >= 229376 ? kTriDefaultVariant : h->n >= 49152 ? kCrowDefaultVariant : 0;
+    if (h->world == 1) return h->n >= 655360 ? kSegDefaultVariant : h->n >= 229376 ? kTriDefaultVariant : h->n >= 49152 ? kCrowDefaultVariant : 0;
     return per >= 262144 ? kTriDefaultVariant : per >= 65536 ? kCrowDefaultVariant : 0;
 }
 
@@ -567,6 +569,7 @@ static int launch_seg(hgb_nbody *h, int variant, NbShard &s, const double *src, 
     a.src = src; a.npad = h->npad; a.n = h->n; a.T = (h->n + 63) / 64; a.seg = s.seg_plan_seg; a.tr = s.seg_plan_rows;
     a.tiles = s.seg_tiles; a.ntiles = s.seg_ntiles; a.ll = s.sym_ll; a.racc = s.seg_racc;
     a.epoch_tag = s.sym_epoch << 21; a.ctl = s.sym_ctl; a.spin_limit = kTriSpinLimit;
+    { const char *e = getenv("HGB_NBODY_SEG_HYST"); a.hyst = e ? atoi(e) : 0; }
     const size_t smem = (size_t)kSymWarps * 6 * 3 * 32 * sizeof(double);
     const int grid = s.dev->sms * 2;
     if (variant == 5242) nbody_seg_kernel<2, 4, 2, true><<<grid, kSymWarps * 32, smem, st>>>(a);
@@ -729,7 +732,12 @@ int hgb_nbody_sym_counters(hgb_nbody *h, unsigned long long *out7) {
     HGB_CUDA(cudaSetDevice(s.dev->device));
     HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
     HGB_CUDA(cudaMemcpy(out7, ctl + 8, 7 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
-    if (getenv("HGB_NBODY_SYM_HIST") && ctl == s.sym_ctl) {   // diagnostic: wait cycles by eighth of the row x quarter of the workers
+    if (getenv("HGB_NBODY_SYM_HIST") && ctl == s.sym_ctl && seg_variant(sym_variant_in_effect(h))) {
+        unsigned long long polled[5] = {0};
+        HGB_CUDA(cudaMemcpy(polled, ctl + 24, sizeof polled, cudaMemcpyDeviceToHost));
+        fprintf(stderr, "seg: chunk opens that had to poll: %llu; by quarter of the blocks: %llu %llu %llu %llu\n", polled[0], polled[1], polled[2],
+                polled[3], polled[4]);
+    } else if (getenv("HGB_NBODY_SYM_HIST") && ctl == s.sym_ctl) {   // diagnostic: wait cycles by eighth of the row x quarter of the workers
         unsigned long long hist[40];
         HGB_CUDA(cudaMemcpy(hist, ctl + 24, sizeof hist, cudaMemcpyDeviceToHost));
         fprintf(stderr, "sym: chunks the predecessor is ahead at a chunk open (0, 1, 2, 3, 4-7, 8-15, 16-31, 32+):");

@@ -73,6 +73,7 @@ struct SegArgs {
     unsigned epoch_tag;
     int *ctl;                 // ctl[0] ticket, ctl[1] range flag, ctl[2] abort flag, ctl[8..] span counters (PROF)
     long long spin_limit;
+    int hyst;                 // chunks a block falls behind its predecessor after catching up with it (0: none)
 };
 
 // poll one tagged word (all lanes together); gives up after the spin limit and raises the abort flag
@@ -119,7 +120,7 @@ nbody_seg_kernel(const __grid_constant__ SegArgs a) {
     ulonglong2 *const ll = a.ll;
     unsigned key = 0;
     int dead = 0;
-    long long t_wait = 0, t_racc = 0, t_fast = 0, t_slow = 0, t_item = 0, n_items = 0, n_chunks = 0;
+    long long t_wait = 0, t_racc = 0, t_fast = 0, t_slow = 0, t_item = 0, n_items = 0, n_chunks = 0, n_polled = 0;
     auto now = [] { return PROF ? clock64() : 0ll; };
 
     for (;;) {
@@ -158,6 +159,7 @@ nbody_seg_kernel(const __grid_constant__ SegArgs a) {
             if (PROF) t_racc += now() - r0;
         }
         int e = (((j_begin - lane) % RING) + RING) % RING;   // ring entry of source j = s - lane at s = j_begin
+        const int last_chunk_of_item = (j_stop - 1) / CH;
 
         int pf_chunk = -1;
         double pf_x = 0.0, pf_y = 0.0, pf_z = 0.0;
@@ -179,15 +181,20 @@ nbody_seg_kernel(const __grid_constant__ SegArgs a) {
             const long long a0 = now();
             if (pf_chunk != c) prefetch_chunk(c);
             if (lower && !__all_sync(FULL, ll_ok(pf_ax, want_tag) && ll_ok(pf_ay, want_tag) && ll_ok(pf_az, want_tag))) {
+                if (PROF) { ++n_polled; if (lane == 0) atomicAdd(reinterpret_cast<unsigned long long *>(a.ctl + 26) + min(3, 4 * w / a.T), 1ull); }
+                // caught up with block w-1: fall a.hyst chunks behind first (a later chunk of the same segment that block
+                // w-1 streams, not one of its own), so that the next prefetches find their words
+                const int ahead = min(min(c + a.hyst, last_chunk_of_item), (w - 1) * R - 1);
+                if (a.hyst > 0 && ahead > c) seg_poll(a, ll + (size_t)ahead * 3 * CH + 2 * CH + lane, want_tag, dead);
                 const ulonglong2 *q = ll + (size_t)c * 3 * CH + lane;
                 pf_ax = seg_poll(a, q, want_tag, dead);
                 pf_ay = seg_poll(a, q + CH, want_tag, dead);
                 pf_az = seg_poll(a, q + 2 * CH, want_tag, dead);
             }
+            if (PROF) { t_wait += now() - a0; ++n_chunks; }   // the tag check (it also waits for the prefetch loads) and the polls
             rx[slot] = pf_x; ry[slot] = pf_y; rz[slot] = pf_z;
             if (lower) { rax[slot] = ll_unpack(pf_ax); ray[slot] = ll_unpack(pf_ay); raz[slot] = ll_unpack(pf_az); }
             __syncwarp();
-            if (PROF) { t_wait += now() - a0; ++n_chunks; }
         };
         auto close_chunk = [&](int c) {
             const int slot = (c % 3) * CH + lane;
@@ -412,6 +419,7 @@ nbody_seg_kernel(const __grid_constant__ SegArgs a) {
     if (PROF && lane == 0) {
         unsigned long long *cnt = reinterpret_cast<unsigned long long *>(a.ctl + 8);
         atomicAdd(cnt + 0, (unsigned long long)t_wait); atomicAdd(cnt + 1, (unsigned long long)t_racc);
+        atomicAdd(reinterpret_cast<unsigned long long *>(a.ctl + 24), (unsigned long long)n_polled);
         atomicAdd(cnt + 2, (unsigned long long)t_item); atomicAdd(cnt + 3, (unsigned long long)t_fast);
         atomicAdd(cnt + 4, (unsigned long long)t_slow); atomicAdd(cnt + 5, (unsigned long long)n_items);
         atomicAdd(cnt + 6, (unsigned long long)n_chunks);

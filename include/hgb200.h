@@ -94,10 +94,12 @@ int hgb_nbody_tune(hgb_nbody *h, int block, int unroll, int warps);
  * 17-25), so the result is bit-identical to hgb_nbody_tune's kernel at 16 instead of 29 FP64
  * instructions per interaction.  variant: 0 = off, 1 = default, else R*100 + U*10 + CTAs per SM;
  * used on single-GPU handles in EXACT mode when n >= min_n (the wavefront needs a large n to fill
- * the GPU).  New handles pick the kernel by bodies per GPU (standard / 3002 / 2002 / 242; env
+ * the GPU).  New handles pick the kernel by bodies per GPU (standard / 3002 / 2002 / 6242; env
  * HGB_NBODY_SYM = 0 | 1 | variant and HGB_NBODY_SYM_MIN_N override); variant 1 here asks for the first generation
  * from min_n up on one GPU; hgb_nbody_tune with a non-zero argument switches the pair-symmetric kernels off.
- * Variants 3000 + C (3002 default; 3010 + C with span counters): csrc/nbody_crow.cuh, a CTA of four warps per row. */
+ * Variants 3000 + C (3002 default; 3010 + C with span counters): csrc/nbody_crow.cuh, a CTA of four warps per row.
+ * Variants 4242 / 6242 (5242 / 7242 with span counters): csrc/nbody_seg.cuh, the first generation's warp on the segmented
+ * schedule, plain / with software-pipelined groups (one GPU). */
 int hgb_nbody_set_symmetric(hgb_nbody *h, int variant, int min_n);
 /* Variants 2000 + C (C = 1..3 CTAs per SM; 2 = 2002; 2010 + C: with clock64 span counters) select the
  * second-generation pair-symmetric kernel (csrc/nbody_tri.cuh): forces evaluated per 32 x 8 minitile, the

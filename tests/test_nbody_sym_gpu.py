@@ -163,12 +163,12 @@ def test_sym_is_ignored_where_it_does_not_apply(hgb):
 
 def test_sym_default_policy(hgb):
     """new one-GPU handles pick the kernel by size (standard < 49152 <= cooperative rows < 229376 <= one warp
-    per row < 786432 <= first generation); an explicit hgb_nbody_tune variant of the standard kernel or FAST
+    per row < 655360 <= segmented first generation); an explicit hgb_nbody_tune variant of the standard kernel or FAST
     mode switch the pair-symmetric kernels off; hgb_nbody_set_symmetric(h, 1, min_n) asks for the first generation"""
     L = hgb.lib()
     if os.environ.get("HGB_NBODY_SYM") or os.environ.get("HGB_NBODY_SYM_MIN_N"):
         pytest.skip("defaults overridden by the environment")
-    for n, want in ((49151, 0), (49152, 3002), (229375, 3002), (229376, 2002), (786431, 2002), (786432, 242)):
+    for n, want in ((49151, 0), (49152, 3002), (229375, 3002), (229376, 2002), (655359, 2002), (655360, 6242)):
         with hgb.nbody.NBody(n) as nb:
             assert L.hgb_nbody_symmetric(nb._h) == want, n
     with hgb.nbody.NBody(393216) as nb:

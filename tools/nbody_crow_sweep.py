@@ -49,6 +49,7 @@ for n in sizes:
         variant, seg, rows, weight = spec[:4]
         flags = spec[4] if len(spec) > 4 else 0
         os.environ["HGB_NBODY_TRI_FLAGS"] = str(flags)      # read by the library at every launch
+        os.environ["HGB_NBODY_SEG_HYST"] = str(flags)
         if seg > n:
             continue
         ms, out, c = run(n, pos, variant, seg, steps=steps, rows=rows, weight=weight)
