@@ -33,7 +33,7 @@ struct NbShard {
     ulonglong2 *tri_ll[2] = {nullptr, nullptr};   // chain words, double-buffered by step parity, 48 B per body each
     ulonglong2 *tri_racc = nullptr;               // row accumulators between the items of a row, 48 B per body
     int2 *tri_tiles = nullptr;                    // this shard's tiles in ticket order
-    int tri_ntiles = 0, tri_plan_seg = 0, tri_plan_rows = 0, tri_plan_weight = 0, tri_plan_deal = 0;
+    int tri_ntiles = 0, tri_plan_seg = 0, tri_plan_rows = 0, tri_plan_weight = 0, tri_plan_deal = 0, tri_plan_rs = 0;
     // first-generation warp on the segmented schedule (nbody_seg.cuh): row sums between items, tiles in ticket order
     ulonglong2 *seg_racc = nullptr;
     int2 *seg_tiles = nullptr;
@@ -198,13 +198,16 @@ static int sym_variant_in_effect(const hgb_nbody *h) {
     // generation on one GPU from min_n up (what the caller asked for), the ladder across GPUs
     const int v = (h->sym_auto == 2 || (h->sym_auto == 1 && h->world > 1)) ? auto_variant(h) : h->sym;
     if (v == 0 || h->n < h->sym_min_n) return 0;
-    if (!tri_variant(v)) return h->world == 1 ? v : 0;   // first generation: one GPU
+    if (!tri_variant(v) && !seg_variant(v)) return h->world == 1 ? v : 0;   // first generation: one GPU
     if (h->world == 1) return v;
     // rows dealt over GPUs: peer-mapped buffers -- of this process (peer-store handles) or of the other ranks (CUDA IPC)
     if (!h->rank_mode) return h->exchange == HGB_EXCHANGE_P2P ? v : 0;
     return h->tri_connected >= 0 ? v : 0;
 }
 static bool sym_applies(const hgb_nbody *h) { return sym_variant_in_effect(h) != 0; }
+// runs through the multi-GPU wavefront framework (peer-mapped double-buffered chain words, polling finish kernel): the second and
+// third generation always, the segmented first generation when its blocks are dealt over several GPUs
+static bool tri_framework(const hgb_nbody *h, int v) { return tri_variant(v) || (seg_variant(v) && h->world > 1); }
 
 // ---- second-generation pair-symmetric step (nbody_tri.cuh) ------------------------------------------
 constexpr int kTriDefaultSeg = 16384;     // sources per item
@@ -214,13 +217,13 @@ constexpr int kTriDefaultSeg = 16384;     // sources per item
 // cooperative rows (nbody_crow_kernel, 4x fewer workers): rows handed out ONE at a time -- rows of a tile take
 // consecutive tickets and then follow each other at the minimum distance, where every small delay of the row
 // above costs a full L2 round trip (profiles/r3i_crow_schedule_*.txt: 1537 vs 1618 ms at N = 2^20)
-static int tri_default_rows(const hgb_nbody *h, int v) { return crow_variant(v) ? (h->world > 1 ? 8 : 1) : h->world > 1 ? 16 : 8; }
-static int tri_default_weight(const hgb_nbody *h, int v) { return crow_variant(v) ? (h->world > 1 ? 32 : 128) : h->world > 1 ? 64 : 32; }
+static int tri_default_rows(const hgb_nbody *h, int v) { return seg_variant(v) ? 4 : crow_variant(v) ? (h->world > 1 ? 8 : 1) : h->world > 1 ? 16 : 8; }
+static int tri_default_weight(const hgb_nbody *h, int v) { return seg_variant(v) ? 64 : crow_variant(v) ? (h->world > 1 ? 32 : 128) : h->world > 1 ? 64 : 32; }
 // rows per turn of a GPU (a multiple of the rows per tile): chain words cross NVLink once per turn.  Across GPUs the
 // single-row hand-out does NOT carry over (8 GPUs, N = 2^20: 1122 ms with rows 1 / weight 128 against 220 ms with
 // rows 8 / weight 32 / turns of 8, profiles/r3k_multi_g8.txt): a GPU then holds only every 8th turn of rows and the
 // ticket order of one GPU no longer follows the anti-diagonal the others are on.
-static int tri_default_deal(const hgb_nbody *h, int v) { return h->world > 1 ? (crow_variant(v) ? 8 : 16) : 1; }
+static int tri_default_deal(const hgb_nbody *h, int v) { return h->world > 1 ? (seg_variant(v) || crow_variant(v) ? 8 : 16) : 1; }   // seg: blocks of 64 targets
 struct TriPlanParams { int seg, tr, weight, deal; };
 static TriPlanParams tri_params(const hgb_nbody *h, int v) {
     TriPlanParams p;
@@ -242,13 +245,14 @@ constexpr long long kTriSpinLimit = 10000000000ll;   // ~5 s of SM clock: a poll
 static int tri_plan(hgb_nbody *h, NbShard &s, int variant) {
     const TriPlanParams pp = tri_params(h, variant);
     const int seg = pp.seg, tr = pp.tr, weight = pp.weight, deal = pp.deal;
-    if (s.tri_tiles && s.tri_plan_seg == seg && s.tri_plan_rows == tr && s.tri_plan_weight == weight && s.tri_plan_deal == deal) return HGB_OK;
-    const int T = (h->n + 31) / 32, TB = (T + tr - 1) / tr;
+    const int RS = seg_variant(variant) ? 64 : 32;   // targets per row (a block of nbody_seg_kernel has two per lane)
+    if (s.tri_tiles && s.tri_plan_seg == seg && s.tri_plan_rows == tr && s.tri_plan_weight == weight && s.tri_plan_deal == deal && s.tri_plan_rs == RS) return HGB_OK;
+    const int T = (h->n + RS - 1) / RS, TB = (T + tr - 1) / tr;
     std::vector<std::pair<long long, int2>> keyed;
     for (int b = 0; b < TB; ++b) {
         if (((long long)b * tr / deal) % h->world != s.index) continue;   // rows I with I / deal = index (mod GPUs)
         const long long last_row = std::min(T - 1, b * tr + tr - 1);
-        const int kmax = (int)(32 * last_row / seg);
+        const int kmax = (int)((long long)RS * last_row / seg);
         for (int k = 0; k <= kmax; ++k) keyed.push_back({((long long)b + (long long)weight * k) * 4096 + k, make_int2(b, k)});
     }
     std::sort(keyed.begin(), keyed.end(), [](const auto &x, const auto &y) { return x.first < y.first; });
@@ -260,7 +264,7 @@ static int tri_plan(hgb_nbody *h, NbShard &s, int variant) {
     HGB_CUDA(cudaMemcpyAsync(s.tri_tiles, tiles.data(), sizeof(int2) * tiles.size(), cudaMemcpyHostToDevice, s.dev->stream));
     HGB_CUDA(cudaStreamSynchronize(s.dev->stream));   // `tiles` goes out of scope
     s.tri_ntiles = (int)tiles.size();
-    s.tri_plan_seg = seg; s.tri_plan_rows = tr; s.tri_plan_weight = weight; s.tri_plan_deal = deal;
+    s.tri_plan_seg = seg; s.tri_plan_rows = tr; s.tri_plan_weight = weight; s.tri_plan_deal = deal; s.tri_plan_rs = RS;
     return HGB_OK;
 }
 
@@ -427,7 +431,8 @@ static int launch_tri_step(hgb_nbody *h, int variant, int cur, int nxt) {
     const unsigned step = h->tri_step++;
     const int parity = step & 1;
     const unsigned epoch_tag = (step % 2047 + 1) << 21;
-    const int seg = h->sh[0].tri_plan_seg, rows = h->sh[0].tri_plan_rows, deal = h->sh[0].tri_plan_deal, T = (h->n + 31) / 32;
+    const int RS = h->sh[0].tri_plan_rs;   // targets per row: 32, or 64 for the segmented first-generation blocks
+    const int seg = h->sh[0].tri_plan_seg, rows = h->sh[0].tri_plan_rows, deal = h->sh[0].tri_plan_deal, T = (h->n + RS - 1) / RS;
     const int ctas = variant % 10;
     const bool prof = (variant / 10) % 10 == 1 || (variant / 10) % 10 == 3;
     for (NbShard &s : h->sh) {
@@ -467,7 +472,25 @@ static int launch_tri_step(hgb_nbody *h, int variant, int cur, int nxt) {
         a.racc = s.tri_racc; a.epoch_tag = epoch_tag; a.ctl = s.tri_ctl; a.spin_limit = kTriSpinLimit;
         const int grid = std::max(1, s.dev->sms * ctas / tri_shards_on_device(h, s));
         int rc = HGB_ERR_ARG;
-        if (crow_variant(variant)) {
+        if (seg_variant(variant)) {
+            SegArgs g;
+            memset(&g, 0, sizeof g);
+            g.src = a.src; g.npad = a.npad; g.n = a.n; g.T = T; g.seg = seg; g.tr = rows; g.tiles = a.tiles; g.ntiles = a.ntiles;
+            g.ll = a.ll; g.racc = a.racc; g.epoch_tag = a.epoch_tag; g.ctl = a.ctl; g.spin_limit = a.spin_limit;
+            { const char *e = getenv("HGB_NBODY_SEG_HYST"); g.hyst = e ? atoi(e) : 0; }
+            g.ll_down = a.ll_down; g.deal = deal; g.npeers = a.npeers; g.range_slot = a.range_slot;
+            for (int p = 0; p < h->world; ++p) g.ctl_all[p] = a.ctl_all[p];
+            const size_t smem = (size_t)kSymWarps * 6 * 3 * 32 * sizeof(double);
+            const int sgrid = std::max(1, s.dev->sms * 2 / tri_shards_on_device(h, s));
+            switch (variant) {
+                case 4242: nbody_seg_kernel<2, 4, 2, false, false><<<sgrid, kSymWarps * 32, smem, s.dev->stream>>>(g); break;
+                case 5242: nbody_seg_kernel<2, 4, 2, true, false><<<sgrid, kSymWarps * 32, smem, s.dev->stream>>>(g); break;
+                case 7242: nbody_seg_kernel<2, 4, 2, true, true><<<sgrid, kSymWarps * 32, smem, s.dev->stream>>>(g); break;
+                default: nbody_seg_kernel<2, 4, 2, false, true><<<sgrid, kSymWarps * 32, smem, s.dev->stream>>>(g); break;
+            }
+            HGB_LAUNCHED();
+            rc = HGB_OK;
+        } else if (crow_variant(variant)) {
             switch (variant) {
                 case 3001: rc = launch_crow_variant<4, 1, false>(a, grid, s.dev->stream); break;
                 case 3002: rc = launch_crow_variant<4, 2, false>(a, grid, s.dev->stream); break;
@@ -570,6 +593,7 @@ static int launch_seg(hgb_nbody *h, int variant, NbShard &s, const double *src, 
     a.tiles = s.seg_tiles; a.ntiles = s.seg_ntiles; a.ll = s.sym_ll; a.racc = s.seg_racc;
     a.epoch_tag = s.sym_epoch << 21; a.ctl = s.sym_ctl; a.spin_limit = kTriSpinLimit;
     { const char *e = getenv("HGB_NBODY_SEG_HYST"); a.hyst = e ? atoi(e) : 0; }
+    a.ll_down = a.ll; a.deal = a.T + 1; a.npeers = 1; a.ctl_all[0] = s.sym_ctl; a.range_slot = 1;   // one GPU: nothing leaves it
     const size_t smem = (size_t)kSymWarps * 6 * 3 * 32 * sizeof(double);
     const int grid = s.dev->sms * 2;
     if (variant == 5242) nbody_seg_kernel<2, 4, 2, true><<<grid, kSymWarps * 32, smem, st>>>(a);
@@ -709,7 +733,7 @@ int hgb_nbody_describe(const hgb_nbody *h, char *buf, int capacity) {
         snprintf(kern, sizeof kern, "nbody_step_kernel<%d,%d,%d,%s>", block, unroll, warps, fast ? "true" : "false");
     }
     const char *xchg = h->world == 1 ? "one GPU, no exchange"
-                     : tri_variant(v) ? (h->rank_mode ? "pair-symmetric: tile-rows of targets dealt round-robin over the ranks, chain words stored into the next rank's buffer over NVLink (CUDA IPC mapping), finished sums read from the last row's rank, no position exchange"
+                     : tri_framework(h, v) ? (h->rank_mode ? "pair-symmetric: tile-rows of targets dealt round-robin over the ranks, chain words stored into the next rank's buffer over NVLink (CUDA IPC mapping), finished sums read from the last row's rank, no position exchange"
                                                       : "pair-symmetric: tile-rows of targets dealt round-robin, chain words stored into the next GPU's buffer over NVLink, finished sums read from the last row's GPU, no position exchange")
                      : h->exchange == HGB_EXCHANGE_P2P ? "targets sharded, results stored into every peer's next state over NVLink (fused epilogue)"
                                                        : "targets sharded, ncclAllGather of positions per step";
@@ -727,7 +751,7 @@ double hgb_nbody_fp64_instr(const hgb_nbody *h) {
 int hgb_nbody_sym_counters(hgb_nbody *h, unsigned long long *out7) {
     HGB_ARG(h && out7, "handle / out");
     NbShard &s = h->sh[0];
-    int *ctl = tri_variant(sym_variant_in_effect(h)) ? s.tri_ctl : s.sym_ctl;
+    int *ctl = tri_framework(h, sym_variant_in_effect(h)) ? s.tri_ctl : s.sym_ctl;
     if (!ctl) { set_error("the pair-symmetric kernel has not run on this handle"); return HGB_ERR_STATE; }
     HGB_CUDA(cudaSetDevice(s.dev->device));
     HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
@@ -913,13 +937,13 @@ static int nb_advance(hgb_nbody *h, int iterations, float *ms, bool dyn) {
         HGB_CUDA(cudaSetDevice(s.dev->device));
         HGB_CUDA(cudaEventRecord(s.dev->ev_begin, s.dev->stream));
     }
-    if (!dyn && tri_variant(sym_variant_in_effect(h))) {
+    if (!dyn && tri_framework(h, sym_variant_in_effect(h))) {
         HGB_TRY(tri_connect(h));   // first use: buffers, peer tables (collective over the ranks); may turn the variant off
         const int v = sym_variant_in_effect(h);
-        if (tri_variant(v)) for (NbShard &s : h->sh) HGB_TRY(tri_plan(h, s, v));
+        if (tri_framework(h, v)) for (NbShard &s : h->sh) HGB_TRY(tri_plan(h, s, v));
     }
     const int variant = dyn ? 0 : sym_variant_in_effect(h);
-    const bool tri = tri_variant(variant);
+    const bool tri = tri_framework(h, variant);
     for (int it = 0; it < iterations; ++it) {
         const int cur = h->cur, nxt = cur ^ 1;
         if (tri) {   // rows dealt over the shards, every shard ends with the whole next state
@@ -989,14 +1013,14 @@ static int nb_advance(hgb_nbody *h, int iterations, float *ms, bool dyn) {
     }
     HGB_CUDA(cudaGetLastError());
     if (ms) *ms = worst;
-    if (seg_variant(variant) && iterations > 0) {
+    if (seg_variant(variant) && !tri && iterations > 0) {
         NbShard &s0 = h->sh[0];
-        int c[8] = {0};
+        int c[32] = {0};
         HGB_CUDA(cudaMemcpy(c, s0.sym_ctl, sizeof c, cudaMemcpyDeviceToHost));
         if (c[2]) {
             set_error("segmented pair-symmetric wavefront abandoned: a hand-off did not arrive within the spin limit; %d tickets of %d items, "
                       "wanted tag epoch %u id %d, found tag %#x, chain word %d, row-sum word %d", c[0], s0.seg_ntiles * s0.seg_plan_rows,
-                      (unsigned)c[6] >> 21, c[6] & 0x1fffff, (unsigned)c[7], c[5], c[4]);
+                      (unsigned)c[6] >> 21, c[6] & 0x1fffff, (unsigned)c[7], c[25], c[26]);
             return HGB_ERR_STATE;
         }
     }

@@ -74,7 +74,19 @@ struct SegArgs {
     int *ctl;                 // ctl[0] ticket, ctl[1] range flag, ctl[2] abort flag, ctl[8..] span counters (PROF)
     long long spin_limit;
     int hyst;                 // chunks a block falls behind its predecessor after catching up with it (0: none)
+    // several GPUs (blocks dealt in turns of `deal`, as in nbody_tri.cuh): where the last block of a turn publishes, who to tell
+    ulonglong2 *ll_down;      // chain-word buffer of the GPU that runs the next turn (== ll on one GPU)
+    int deal;                 // blocks per turn of a GPU
+    int npeers;
+    int *ctl_all[kMaxPeers];  // every GPU's ctl: range and abort flags are raised everywhere
+    int range_slot;           // ctl index of this step's range flag
 };
+
+// raise flag ctl[which] on every GPU (range flag: before the words computed from the operand are published)
+__device__ __noinline__ void seg_raise(const SegArgs &a, int which) {
+    for (int p = 0; p < a.npeers; ++p) *reinterpret_cast<volatile int *>(a.ctl_all[p] + which) = 1;
+    __threadfence_system();
+}
 
 // poll one tagged word (all lanes together); gives up after the spin limit and raises the abort flag
 __device__ __noinline__ ulonglong2 seg_poll(const SegArgs &a, const ulonglong2 *q, unsigned tag, int &dead) {
@@ -85,11 +97,11 @@ __device__ __noinline__ ulonglong2 seg_poll(const SegArgs &a, const ulonglong2 *
         if (__all_sync(0xffffffffu, ll_ok(w, tag))) break;
         bool g = *reinterpret_cast<volatile int *>(a.ctl + 2) != 0;
         if (!g && clock64() - t0 > a.spin_limit) {
-            *reinterpret_cast<volatile int *>(a.ctl + 2) = 1;
             if ((threadIdx.x & 31) == 0 && atomicCAS(a.ctl + 3, 0, 1) == 0) {
                 a.ctl[6] = (int)tag; a.ctl[7] = (int)(w.x >> 32);
-                a.ctl[5] = (int)(q - a.ll); a.ctl[4] = (int)(q - a.racc);
+                a.ctl[25] = (int)(q - a.ll); a.ctl[26] = (int)(q - a.racc);
             }
+            seg_raise(a, 2);
             g = true;
         }
         dead = __any_sync(0xffffffffu, g);
@@ -196,10 +208,16 @@ nbody_seg_kernel(const __grid_constant__ SegArgs a) {
             if (lower) { rax[slot] = ll_unpack(pf_ax); ray[slot] = ll_unpack(pf_ay); raz[slot] = ll_unpack(pf_az); }
             __syncwarp();
         };
+        // block w+1 reads what this block publishes: here, or on the GPU of the next turn; the last block's words are the sums
+        ulonglong2 *const pub = (w % a.deal == a.deal - 1 && w != a.T - 1) ? a.ll_down : ll;
+        auto check_range = [&]() {   // raised everywhere BEFORE the words computed from such an operand are published
+            if (__any_sync(FULL, key >= kRangeLimit)) { seg_raise(a, a.range_slot); key = 0; }
+        };
         auto close_chunk = [&](int c) {
             const int slot = (c % 3) * CH + lane;
             __syncwarp();
-            ulonglong2 *q = ll + (size_t)c * 3 * CH + lane;
+            check_range();
+            ulonglong2 *q = pub + (size_t)c * 3 * CH + lane;
             ll_store(q, ll_pack(rax[slot], my_tag));
             ll_store(q + CH, ll_pack(ray[slot], my_tag));
             ll_store(q + 2 * CH, ll_pack(raz[slot], my_tag));
@@ -405,6 +423,7 @@ nbody_seg_kernel(const __grid_constant__ SegArgs a) {
         if (last_chunk - 1 >= first_chunk && !early_closed) close_chunk(last_chunk - 1);
         close_chunk(last_chunk);
         if (!last_item) {   // hand the block's row sums to item (w, k+1)
+            check_range();
             ulonglong2 *q = a.racc + (size_t)w * (3 * R * 32) + lane;
             const unsigned tag = a.epoch_tag | (unsigned)(k + 1);
 #pragma unroll
@@ -424,7 +443,7 @@ nbody_seg_kernel(const __grid_constant__ SegArgs a) {
         atomicAdd(cnt + 4, (unsigned long long)t_slow); atomicAdd(cnt + 5, (unsigned long long)n_items);
         atomicAdd(cnt + 6, (unsigned long long)n_chunks);
     }
-    if (key >= kRangeLimit) a.ctl[1] = 1;
+    if (__any_sync(FULL, key >= kRangeLimit)) seg_raise(a, a.range_slot);
 }
 
 }  // namespace hgb

@@ -45,7 +45,7 @@
 namespace hgb {
 
 constexpr int kTriWarps = 4;          // warps (independent workers) per CTA
-constexpr int kTriCtlInts = 32;       // ctl[0] ticket, ctl[2] abort flag, ctl[4], ctl[5] range flag of even / odd steps, ctl[8..19] profiling, ctl[3], [6], [7], [24..26] what an abandoned poll waited for
+constexpr int kTriCtlInts = 64;       // ctl[0] ticket, ctl[2] abort flag, ctl[4], ctl[5] range flag of even / odd steps, ctl[8..19] profiling, ctl[3], [6], [7], [24..26] what an abandoned poll waited for
 constexpr int kTbPitch = 34;          // doubles per row of the transposed buffer (16-byte rows, conflict-free LDS.128)
 constexpr int kTriWarpDoubles = 2 * 3 * 32 + 2 * 24 * kTbPitch + 32;   // ring + 2 transposed buffers + chain seeds
 constexpr size_t kTriSmem = (size_t)kTriWarps * kTriWarpDoubles * sizeof(double);

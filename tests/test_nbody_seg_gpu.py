@@ -17,9 +17,10 @@ def sha(a):
     return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
 
 
-def seg_step(hgb, pos, iters, variant=4242, seg=0, rows=0, weight=0, want_prev=False):
-    with hgb.nbody.NBody(pos.shape[0]) as nb:
-        nb.symmetric(variant, 0).segment(seg, rows, weight).upload(pos)
+def seg_step(hgb, pos, iters, variant=4242, seg=0, rows=0, weight=0, want_prev=False, ngpus=1, deal=0):
+    kind = hgb.EXCHANGE_P2P if ngpus > 1 else hgb.EXCHANGE_NCCL
+    with hgb.nbody.NBody(pos.shape[0], ngpus=ngpus, exchange=kind) as nb:
+        nb.symmetric(variant, 0).segment(seg, rows, weight).deal(deal).upload(pos)
         assert hgb.lib().hgb_nbody_symmetric(nb._h) == variant
         assert nb.describe()[0].startswith("nbody_seg_kernel")
         nb.step(iters)
@@ -123,3 +124,29 @@ def test_seg_full_size_1m_all_bodies_equal_the_standard_kernel(hgb):
         got = seg_step(hgb, pos, 1, variant)
         assert np.array_equal(got[targets], want)
         assert np.array_equal(got, std)
+
+
+def _gpu_counts(hgb, monkeypatch):
+    g = min(hgb.lib().hgb_device_count(), 8)
+    if g < 2:
+        monkeypatch.setenv("HGB_VIRTUAL_GPUS", "4")
+        return [2, 3, 4]
+    return sorted({2, g})
+
+
+@pytest.mark.parametrize("n,iters,seg", [(5000, 3, 64), (2048, 2, 32), (70001, 2, 1024), (100, 2, 32), (40000, 1, 0)])
+def test_seg_blocks_dealt_over_gpus_are_bit_identical(hgb, monkeypatch, n, iters, seg):
+    """blocks of 64 targets dealt over the GPUs in turns (peer-mapped chain words, polling finish kernel): same bits"""
+    from oracle import port
+    counts = _gpu_counts(hgb, monkeypatch)
+    pos = synth.plummer(n, seed=n)
+    one_cur, one_prev = seg_step(hgb, pos, iters, 6242, seg=seg, want_prev=True)
+    if n <= 5000:
+        want_cur, want_prev = oracle_run(pos, iters)
+        assert np.array_equal(one_cur, want_cur) and np.array_equal(one_prev, want_prev)
+    sample = np.random.default_rng(n).choice(n, size=min(n, 96), replace=False).astype(np.int32)
+    assert np.array_equal(one_cur[sample], port.nbody_accel_subset(one_prev, sample))
+    for g in counts:
+        for variant, rows, deal in ((6242, 0, 0), (6242, 1, 1), (4242, 2, 6), (7242, 3, 3)):
+            cur, prev = seg_step(hgb, pos, iters, variant, seg=seg, rows=rows, weight=max(1, rows), want_prev=True, ngpus=g, deal=deal)
+            assert np.array_equal(cur, one_cur) and np.array_equal(prev, one_prev), (g, variant, rows, deal)

@@ -53,7 +53,9 @@ def main():
     for variant, n, iters, seg, rows, weight in ((2002, 5000, 3, 256, 2, 0), (2002, 2048, 5, 64, 1, 4), (2002, 70001, 2, 4096, 4, 0),
                                                  (2002, 1 << 17, 3, 0, 0, 0), (2002, 33, 2, 32, 1, 1), (2002, 1 << 15, 4, 1024, 8, 2),
                                                  (3002, 5000, 3, 256, 2, 0), (3002, 2048, 5, 96, 1, 4), (3002, 70001, 2, 4096, 4, 0),
-                                                 (3002, 1 << 17, 3, 0, 0, 0), (3002, 33, 2, 32, 1, 1), (3002, 1 << 15, 4, 1056, 8, 2)):
+                                                 (3002, 1 << 17, 3, 0, 0, 0), (3002, 33, 2, 32, 1, 1), (3002, 1 << 15, 4, 1056, 8, 2),
+                                                 (6242, 5000, 3, 256, 2, 0), (6242, 2048, 5, 96, 1, 4), (6242, 70001, 2, 4096, 4, 0),
+                                                 (6242, 1 << 17, 3, 0, 0, 0), (6242, 65, 2, 32, 1, 1), (6242, 1 << 15, 4, 1056, 8, 2)):
         pos = synth.plummer(n, seed=n + 1)
         with H.nbody.NBody(n, ngpus=None, mode=H.NBODY_EXACT) as nb:
             nb.symmetric(variant, 0).segment(seg, rows, weight)
