@@ -719,8 +719,10 @@ int hgb_nbody_describe(const hgb_nbody *h, char *buf, int capacity) {
                  tri_params(h, v).tr, tri_params(h, v).weight);
     } else if (v) {
         if (seg_variant(v))
-            snprintf(kern, sizeof kern, "nbody_seg_kernel<2,4,2%s> seg=%d rows=%d weight=%d", v >= 6000 ? ",pipelined" : "", h->tri_seg > 0 ? h->tri_seg : kSegDefaultSeg,
-                     h->tri_rows > 0 ? h->tri_rows : kSegDefaultRows, h->tri_weight > 0 ? h->tri_weight : kSegDefaultWeight);
+            snprintf(kern, sizeof kern, "nbody_seg_kernel<2,4,2%s> seg=%d rows=%d weight=%d", v >= 6000 ? ",pipelined" : "",
+                     h->world > 1 ? tri_params(h, v).seg : h->tri_seg > 0 ? h->tri_seg : kSegDefaultSeg,
+                     h->world > 1 ? tri_params(h, v).tr : h->tri_rows > 0 ? h->tri_rows : kSegDefaultRows,
+                     h->world > 1 ? tri_params(h, v).weight : h->tri_weight > 0 ? h->tri_weight : kSegDefaultWeight);
         else
             snprintf(kern, sizeof kern, "nbody_sym_kernel<%d,%d,%d>", v / 100, v / 10 % 10, v % 10);
     } else {
