@@ -171,6 +171,16 @@ nbody_seg_kernel(const __grid_constant__ SegArgs a) {
             if (PROF) t_racc += now() - r0;
         }
         int e = (((j_begin - lane) % RING) + RING) % RING;   // ring entry of source j = s - lane at s = j_begin
+        if (PROF && lane == 0 && w > 0 && j_begin / CH + 40 < min((w - 1) * R, (j_stop - 1) / CH)) {
+            // diagnostic: how many chunks of this segment block w-1 has already published when this item starts
+            int ahead = 0;
+            for (int kk = 0; kk < 32; ++kk) {
+                const ulonglong2 t = ll_load(a.ll + (size_t)(j_begin / CH + kk) * 3 * CH);
+                if ((unsigned)(t.x >> 32) != (a.epoch_tag | (unsigned)w)) break;
+                ahead = kk + 1;
+            }
+            atomicAdd(reinterpret_cast<unsigned long long *>(a.ctl + 40) + (ahead >= 32 ? 7 : ahead >= 16 ? 6 : ahead >= 8 ? 5 : ahead >= 4 ? 4 : ahead), 1ull);
+        }
         const int last_chunk_of_item = (j_stop - 1) / CH;
 
         int pf_chunk = -1;
@@ -198,10 +208,16 @@ nbody_seg_kernel(const __grid_constant__ SegArgs a) {
                 // w-1 streams, not one of its own), so that the next prefetches find their words
                 const int ahead = min(min(c + a.hyst, last_chunk_of_item), (w - 1) * R - 1);
                 if (a.hyst > 0 && ahead > c) seg_poll(a, ll + (size_t)ahead * 3 * CH + 2 * CH + lane, want_tag, dead);
+                // the three words of this lane's entry together, inline: ONE round trip per attempt (a block that has caught up
+                // with the one above pays this at every chunk -- three polls one after the other cost three round trips)
                 const ulonglong2 *q = ll + (size_t)c * 3 * CH + lane;
-                pf_ax = seg_poll(a, q, want_tag, dead);
-                pf_ay = seg_poll(a, q + CH, want_tag, dead);
-                pf_az = seg_poll(a, q + 2 * CH, want_tag, dead);
+                const long long t0 = clock64();
+                while (!dead) {
+                    pf_ax = ll_load(q); pf_ay = ll_load(q + CH); pf_az = ll_load(q + 2 * CH);
+                    if (__all_sync(FULL, ll_ok(pf_ax, want_tag) && ll_ok(pf_ay, want_tag) && ll_ok(pf_az, want_tag))) break;
+                    if (clock64() - t0 > a.spin_limit || *reinterpret_cast<volatile int *>(a.ctl + 2) != 0)
+                        pf_ax = seg_poll(a, q, want_tag, dead);   // out of line: gives up, records what never came, raises the abort flag
+                }
             }
             if (PROF) { t_wait += now() - a0; ++n_chunks; }   // the tag check (it also waits for the prefetch loads) and the polls
             rx[slot] = pf_x; ry[slot] = pf_y; rz[slot] = pf_z;

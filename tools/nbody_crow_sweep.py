@@ -29,7 +29,7 @@ def run(n, pos, variant, seg=0, steps=1, rows=0, weight=0):
         ms = nb.step(steps) / steps
         out = nb.download()
         counters = None
-        if (2000 <= variant < 4000 and (variant // 10) % 10 in (1, 3)) or variant in (5242, 7242):
+        if (2000 <= variant < 4000 and (variant // 10) % 10 in (1, 3)) or variant in (5242, 7242, 7241):
             c = (C.c_ulonglong * 7)()
             H._abi.check(H.lib().hgb_nbody_sym_counters(nb._h, c))
             counters = list(c)
@@ -54,7 +54,7 @@ for n in sizes:
             continue
         ms, out, c = run(n, pos, variant, seg, steps=steps, rows=rows, weight=weight)
         extra = ""
-        if c and variant in (5242, 7242):
+        if c and variant in (5242, 7242, 7241):
             tot = max(1, c[2])
             extra = (f"  of item time: chain-word waits {100.0 * c[0] / tot:.1f} % row-sum waits {100.0 * c[1] / tot:.1f} % predicate-free loop "
                      f"{100.0 * c[3] / tot:.1f} % predicated groups {100.0 * c[4] / tot:.1f} %; items {c[5]}, loop cycles per chunk {c[3] / max(1, c[6]):.0f}")
