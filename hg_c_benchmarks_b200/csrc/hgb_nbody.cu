@@ -139,7 +139,7 @@ static bool crow_variant(int v) {
 static bool tri_variant(int v) { return (v >= 2001 && v <= 2023 && (v % 10) >= 1 && (v % 10) <= 3) || crow_variant(v); }
 
 // 4242 (5242 with span counters): the first generation's systolic warp (R = 2, U = 4, 2 CTAs per SM) on the segmented schedule
-static bool seg_variant(int v) { return v == 4242 || v == 5242 || v == 6242 || v == 7242 || v == 6241 || v == 7241; }   // ...1: one CTA per SM (diagnostic)   // 6242 / 7242: pipelined groups
+static bool seg_variant(int v) { return v == 4242 || v == 5242 || v == 6242 || v == 7242 || v == 6241 || v == 7241 || v == 6223 || v == 6224; }   // ...1: one CTA per SM (diagnostic)   // 6242 / 7242: pipelined groups
 
 static bool sym_variant_known(int v) {
     if (tri_variant(v) || seg_variant(v)) return true;
@@ -596,7 +596,9 @@ static int launch_seg(hgb_nbody *h, int variant, NbShard &s, const double *src, 
     a.ll_down = a.ll; a.deal = a.T + 1; a.npeers = 1; a.ctl_all[0] = s.sym_ctl; a.range_slot = 1;   // one GPU: nothing leaves it
     const size_t smem = (size_t)kSymWarps * 6 * 3 * 32 * sizeof(double);
     const int grid = s.dev->sms * 2;
-    if (variant == 6241) nbody_seg_kernel<2, 4, 1, false, true><<<s.dev->sms, kSymWarps * 32, smem, st>>>(a);
+    if (variant == 6223) nbody_seg_kernel<2, 2, 3, false, true><<<s.dev->sms * 3, kSymWarps * 32, smem, st>>>(a);
+    else if (variant == 6224) nbody_seg_kernel<2, 2, 4, false, true><<<s.dev->sms * 4, kSymWarps * 32, smem, st>>>(a);
+    else if (variant == 6241) nbody_seg_kernel<2, 4, 1, false, true><<<s.dev->sms, kSymWarps * 32, smem, st>>>(a);
     else if (variant == 7241) nbody_seg_kernel<2, 4, 1, true, true><<<s.dev->sms, kSymWarps * 32, smem, st>>>(a);
     else if (variant == 5242) nbody_seg_kernel<2, 4, 2, true><<<grid, kSymWarps * 32, smem, st>>>(a);
     else if (variant == 6242) nbody_seg_kernel<2, 4, 2, false, true><<<grid, kSymWarps * 32, smem, st>>>(a);

@@ -119,7 +119,7 @@ __device__ __noinline__ ulonglong2 seg_poll(const SegArgs &a, const ulonglong2 *
 template <int R, int U, int CTAS, bool PROF = false, bool PIPE = false>
 __global__ void __launch_bounds__(kSymWarps * 32, CTAS)
 nbody_seg_kernel(const __grid_constant__ SegArgs a) {
-    static_assert(!PIPE || U == 4, "the pipelined group weaves exactly four steps into the force stages");
+    static_assert(!PIPE || U == 4 || U == 2, "the pipelined group weaves four (or two) steps into the force stages");
     constexpr int BS = 32 * R, CH = 32, RING = 3 * CH;
     constexpr unsigned FULL = 0xffffffffu;
     static_assert(CH % U == 0, "groups of U steps must not straddle a chunk boundary");
@@ -372,6 +372,11 @@ nbody_seg_kernel(const __grid_constant__ SegArgs a) {
             double ux = rax[esp[0]], uy = ray[esp[0]], uz = raz[esp[0]];
             pair_forces_hooked<R * U>(qx, qy, qz, jx, jy, jz, vnx, vny, vnz, key, [&](auto st) {
                 constexpr int S = decltype(st)::value;
+                if constexpr (U == 2) {
+                    if constexpr (S == 4) { rmw_apply(allv, esp, 0, vpx, vpy, vpz, ux, uy, uz); ux = rax[esp[1]]; uy = ray[esp[1]]; uz = raz[esp[1]]; }
+                    if constexpr (S == 13) { rmw_apply(allv, esp, 1, vpx, vpy, vpz, ux, uy, uz); }
+                    return;
+                }
                 if constexpr (S == 1) { rmw_apply(allv, esp, 0, vpx, vpy, vpz, ux, uy, uz); ux = rax[esp[1]]; uy = ray[esp[1]]; uz = raz[esp[1]]; }
                 if constexpr (S == 6) { rmw_apply(allv, esp, 1, vpx, vpy, vpz, ux, uy, uz); ux = rax[esp[2]]; uy = ray[esp[2]]; uz = raz[esp[2]]; }
                 if constexpr (S == 11) { rmw_apply(allv, esp, 2, vpx, vpy, vpz, ux, uy, uz); ux = rax[esp[3]]; uy = ray[esp[3]]; uz = raz[esp[3]]; }
