@@ -50,6 +50,8 @@ for g in gs:
     grid = [(2002, 16384, r, w) for r in (16, 32, 64) for w in (32, 64, 128, 256)] + [(2002, 8192, r, w) for r in (16, 32) for w in (64, 128)]
     if os.environ.get("TRI_GRID") == "small":
         grid = [(2002, 16384, 8, 32), (2002, 16384, 16, 32), (2002, 16384, 16, 64), (2002, 8192, 16, 32), (2003, 16384, 16, 32)]
+    if os.environ.get("TRI_GRID") == "policy4":
+        grid = [(2002, 16384, 16, 64, 16), (2002, 16384, 8, 64, 8), (3002, 0, 0, 0, 0), (3002, 16384, 8, 32, 16), (6242, 0, 0, 0, 0)]
     if os.environ.get("TRI_GRID") == "seg":
         grid = [(2002, 16384, 16, 64, 16), (6242, 0, 0, 0, 0), (6242, 16384, 2, 128, 8), (6242, 16384, 8, 32, 8), (6242, 16384, 4, 64, 16),
                 (6242, 32768, 4, 64, 8), (6242, 16384, 4, 128, 4), (3002, 0, 0, 0, 0)]
@@ -63,7 +65,7 @@ for g in gs:
         print(f"g={g} n={n} {'crow' if variant >= 3000 else 'tri'} {variant} seg={seg:6d} rows={rows:3d} weight={weight:3d} deal={deal:3d}: {ms:9.3f} ms  "
               f"{n * n / (ms * 1e-3):.4e} inter/s  same={np.array_equal(out, ref)}  [{what[0]}]", flush=True)
     crow = os.environ.get("TRI_GRID") == "crow"
-    if os.environ.get("TRI_GRID") == "seg":
+    if os.environ.get("TRI_GRID") in ("seg", "policy4"):
         continue
     ms, out, c, _ = run(g, 3012 if crow else 2012, 16384, 8 if crow else 16, 32 if crow else 64, steps=1, deal=8 if crow else 16)
     tot = max(1, c[2])
