@@ -227,7 +227,8 @@ static int tri_default_deal(const hgb_nbody *h, int v) { return h->world > 1 ? (
 struct TriPlanParams { int seg, tr, weight, deal; };
 static TriPlanParams tri_params(const hgb_nbody *h, int v) {
     TriPlanParams p;
-    p.seg = h->tri_seg > 0 ? h->tri_seg : kTriDefaultSeg;
+    // cooperative rows on one GPU: 8192-source items (7.93 vs 8.13 ms at 64k, 26.6 vs 26.7 at 128k, 1527 vs 1537 at 2^20)
+    p.seg = h->tri_seg > 0 ? h->tri_seg : (crow_variant(v) && h->world == 1) ? 8192 : kTriDefaultSeg;
     p.tr = h->tri_rows > 0 ? h->tri_rows : tri_default_rows(h, v);
     p.weight = h->tri_weight > 0 ? h->tri_weight : tri_default_weight(h, v);
     p.deal = h->tri_deal > 0 ? h->tri_deal : std::max(p.tr, tri_default_deal(h, v));
