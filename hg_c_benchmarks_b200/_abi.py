@@ -57,6 +57,7 @@ SIGNATURES = {
     "hgb_nbody_download": (C.c_int, [_vp, _dp, _dp]),
     "hgb_nbody_accel_subset": (C.c_int, [_vp, _ip, C.c_int, _dp]),
     "hgb_nbody_energy": (C.c_int, [_vp, _dp]),
+    "hgb_nbody_energy_static": (C.c_int, [_vp, C.c_int, _vp, _vp]),   # device pointers + cudaStream_t
     "hgb_nbody_set_dynamics": (C.c_int, [_vp, _dp, _dp, C.c_double]),
     "hgb_nbody_integrate": (C.c_int, [_vp, C.c_int, _fp]),
     "hgb_nbody_download_velocities": (C.c_int, [_vp, _dp]),

@@ -134,6 +134,32 @@ int hgb_nbody_download(hgb_nbody *h, double *cur_aos, double *prev_aos); /* eith
 int hgb_nbody_accel_subset(hgb_nbody *h, const int *targets, int count, double *out_aos);
 /* extension, no reference counterpart: U = -G sum_{i<j} (|d|^2+EPS)^(-1/2) */
 int hgb_nbody_energy(hgb_nbody *h, double *energy);
+/* The same potential energy for callers that may not allocate device memory.  No counterpart in the
+ * reference (it has no energy at all, and nothing of it runs on a GPU).
+ *
+ * Every other entry point needs a handle, and making one calls cudaMalloc.  That is not open to an
+ * in-situ hook in a host code that gave all of the GPU's memory to its own pool at start-up (the
+ * cudaMalloc would fail), to a monitoring call made while that code's step loop is in flight
+ * (cudaMalloc / cudaFree synchronise the whole device and stall it), or to a plugin that may only
+ * touch device pointers it was handed.  This call allocates and frees nothing, on the device or in
+ * pinned host memory, and copies nothing:
+ *   pos_aos_dev  n bodies as Float3D AoS (x, y, z doubles; src/nbody/nbody-util.h), in DEVICE memory
+ *   energy_dev   one double in DEVICE memory, written with U
+ *   stream       a cudaStream_t (NULL = the default stream) of the CURRENT device; both kernels are
+ *                queued on it and the call returns without waiting -- read *energy_dev after that
+ *                stream has been synchronised.  The pointers must be usable from the current device.
+ * The per-block partial sums go to a fixed 64 KiB array built into the library (each GPU that loads
+ * the library carries it until the process exits), which is why n is limited:
+ * n > HGB_STATIC_ENERGY_MAX_BODIES is refused with HGB_ERR_ARG, nothing launched.
+ * - The first call on each device looks that array's address up (cudaGetSymbolAddress, which may
+ *   load the module); make that first call before starting any stream capture.
+ * - All calls on a device share the array.  It is never cleared and need not be (each call writes
+ *   every slot it later reads), but two calls that overlap on the GPU -- different streams, or
+ *   different host threads -- overwrite each other's partials and both results are garbage.
+ *   Order such calls on one stream or with events.
+ * On one GPU the value is bit-identical to hgb_nbody_energy of the same positions. */
+#define HGB_STATIC_ENERGY_MAX_BODIES 1048576
+int hgb_nbody_energy_static(const double *pos_aos_dev, int n, double *energy_dev, void *stream);
 /* ---- nbody: integrator extension --------------------
  * The reference moves positions only (buffer[i] = G*acc, src/nbody/nbody-run.c:22-24) and has no
  * velocity, mass, dt or energy.  These entry points add them as a separate, clearly non-reference
