@@ -189,7 +189,7 @@ def set_streaming(chunk_rows=1):
 
 
 def unpin():
-    """release the page-lock registrations hgb_conv_run keeps on caller buffers (before freeing them)"""
+    """no longer needed: hgb_conv_run releases its page-lock registrations before it returns"""
     check(lib().hgb_conv_unpin())
 
 

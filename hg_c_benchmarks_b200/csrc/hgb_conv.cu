@@ -748,9 +748,12 @@ void pipe_free() {
 }
 
 // async copies overlap only from page-locked memory: is [ptr, ptr+bytes) page-locked already (cudaHostAlloc,
-// torch pinned memory, an earlier registration)?  Otherwise register it and remember (slot 0: cur, 1: prev).
+// torch pinned memory, the caller's own cudaHostRegister)?  Then nothing to do.  Otherwise register it for THIS
+// call only (slot 0: cur, 1: prev): conv_run_streamed drops the registration before it returns, on every path,
+// because the caller is free to free() the buffer the moment hgb_conv_run is back (the reference's
+// run_on_padded_image callers do) and a registration that outlives its pages poisons the next buffer malloc
+// places at the same address.
 int pipe_pin(int slot, void *ptr, size_t bytes) {
-    if (g_pipe.reg[slot] == ptr && g_pipe.reg_bytes[slot] >= bytes) return HGB_OK;
     cudaPointerAttributes at;
     if (cudaPointerGetAttributes(&at, ptr) == cudaSuccess && at.type == cudaMemoryTypeHost) {
         cudaPointerAttributes end;
@@ -836,12 +839,31 @@ static int stream_plan(int inner_w, int inner_h, int padding, int iterations, in
     return 1;
 }
 
+static int conv_run_streamed_pinned(double *cur, double *prev, int W, int H, int p, const double *kernel, int kw,
+                                    int kh, int iterations, int Hs);
+
+// page-lock what is not page-locked yet, run, and give the registrations back before returning
 static int conv_run_streamed(double *cur, double *prev, int W, int H, int p, const double *kernel, int kw, int kh,
                              int iterations, int Hs) {
+    const size_t bytes = (size_t)H * ((size_t)W + 2 * p) * sizeof(double);
+    int rc = pipe_pin(0, cur, bytes);
+    if (rc == HGB_OK && prev) rc = pipe_pin(1, prev, bytes);
+    if (rc == HGB_OK) {
+        rc = conv_run_streamed_pinned(cur, prev, W, H, p, kernel, kw, kh, iterations, Hs);
+        if (rc != HGB_OK) {   // copies from / to the caller's pages may still be queued: drain before unpinning
+            if (g_pipe.events) { cudaStreamSynchronize(g_pipe.s_in); cudaStreamSynchronize(g_pipe.s_out); }
+            if (g_pipe.sub) cudaStreamSynchronize(g_pipe.sub->sh[0].dev->stream);
+            (void)cudaGetLastError();
+        }
+    }
+    pipe_unpin();
+    return rc;
+}
+
+static int conv_run_streamed_pinned(double *cur, double *prev, int W, int H, int p, const double *kernel, int kw,
+                                    int kh, int iterations, int Hs) {
     const size_t hp = (size_t)W + 2 * p;
     const int F = iterations * p;
-    if (pipe_pin(0, cur, (size_t)H * hp * sizeof(double)) != HGB_OK) return HGB_ERR_STATE;
-    if (prev && pipe_pin(1, prev, (size_t)H * hp * sizeof(double)) != HGB_OK) return HGB_ERR_STATE;
     HGB_TRY(pipe_setup(W, Hs, p));
     CvPipe &P = g_pipe;
     hgb_conv *sub = P.sub;

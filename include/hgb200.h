@@ -213,9 +213,13 @@ int hgb_set_conv_mode(int mode);
  * iterations of other chunks (bit-identical: chunks overlap by iterations*padding rows).  `prev` may be
  * NULL when state n-1 is not wanted (halves the device-to-host traffic).  chunk_rows: 0 = never stream,
  * 1 = automatic (default; env HGB_CONV_STREAM_ROWS), else valid rows per chunk.  Asynchronous copies need
- * page-locked memory: buffers that are not page-locked yet are registered (cudaHostRegister) and stay so
- * across calls; call hgb_conv_unpin() (or hgb_finalize()) BEFORE freeing them. */
+ * page-locked memory: buffers that are not page-locked yet are registered (cudaHostRegister) for the
+ * duration of the call and released before it returns, so the caller may free them right away (as
+ * run_on_padded_image's callers do).  Registering costs time on every call: a caller that reuses its
+ * buffers should page-lock them itself (cudaHostAlloc / cudaHostRegister / torch pinned memory), which
+ * the library detects and leaves alone. */
 int hgb_set_conv_streaming(int chunk_rows);
+/* kept for callers of the earlier ABI, where registrations outlived the call; nothing is left to release */
 int hgb_conv_unpin(void);
 
 /* ---- convolution: device-resident ------------------------------------- */

@@ -484,3 +484,27 @@ def test_streamed_run_keeps_the_drop_in_semantics(hgb):
     finally:
         hgb.convolution.set_streaming(1)
         hgb.convolution.unpin()
+
+
+def test_streamed_runs_on_buffers_freed_between_calls(hgb):
+    """the reference's run_on_padded_image callers (and the shim) free cur/prev as soon as the call is back and
+    allocate fresh ones for the next image; malloc tends to hand the same address out again.  No unpin between
+    the calls: a page-lock registration that outlived the first buffers would make the second call copy through
+    dead mappings."""
+    from oracle import port
+    w, h, p, it = 700, 3000, 1, 2                                  # 2 x 16.8 MB: mmap'ed, unmapped on free
+    kern = synth.kernel_dense(3)
+    seen = set()
+    try:
+        hgb.convolution.set_streaming(200)
+        for seed in (5, 6, 7):
+            img = synth.add_padding(synth.image_float(w, h, seed=seed), p)
+            want_c, want_p = img.copy(), np.zeros_like(img)
+            port.conv_run(want_c, want_p, w, h, p, kern, it)
+            cur, prev = img.copy(), np.full_like(img, -1.0)
+            seen.add((cur.ctypes.data, prev.ctypes.data))
+            hgb.convolution.run_flat(cur, prev, w, h, p, kern, it)
+            assert np.array_equal(cur, want_c) and np.array_equal(prev, want_p), seed
+            del cur, prev, img, want_c, want_p
+    finally:
+        hgb.convolution.set_streaming(1)
