@@ -58,6 +58,9 @@ struct hgb_nbody {
     int tri_deal = 0;       // ... rows per turn of a GPU (0 = default)
     unsigned tri_step = 0;  // steps run with it so far (epoch and buffer parity)
     int tri_status = 0;     // abort flag read back after the last advance
+    int seg_hyst = 0;       // HGB_NBODY_SEG_HYST, read once when the handle is made
+    int seg_inject_abort = -1;   // HGB_NBODY_SEG_INJECT_ABORT=k (test aid): raise the abort flag before one-GPU segmented step k
+    unsigned seg_step = 0;  // one-GPU segmented steps launched on this handle so far
     // chain-word buffers and control words of every shard as THIS process addresses them (own allocations,
     // peer allocations of the same process, or cudaIpcOpenMemHandle mappings of the other ranks')
     ulonglong2 *tri_peer_ll[2][kMaxPeers] = {};
@@ -478,7 +481,7 @@ static int launch_tri_step(hgb_nbody *h, int variant, int cur, int nxt) {
             memset(&g, 0, sizeof g);
             g.src = a.src; g.npad = a.npad; g.n = a.n; g.T = T; g.seg = seg; g.tr = rows; g.tiles = a.tiles; g.ntiles = a.ntiles;
             g.ll = a.ll; g.racc = a.racc; g.epoch_tag = a.epoch_tag; g.ctl = a.ctl; g.spin_limit = a.spin_limit;
-            { const char *e = getenv("HGB_NBODY_SEG_HYST"); g.hyst = e ? atoi(e) : 0; }
+            g.hyst = h->seg_hyst;
             g.ll_down = a.ll_down; g.deal = deal; g.npeers = a.npeers; g.range_slot = a.range_slot;
             for (int p = 0; p < h->world; ++p) g.ctl_all[p] = a.ctl_all[p];
             const size_t smem = (size_t)kSymWarps * 6 * 3 * 32 * sizeof(double);
@@ -574,10 +577,19 @@ static int seg_plan(hgb_nbody *h, NbShard &s) {
     return HGB_OK;
 }
 
+// ctl[0 .. count) = 0 unless the abort flag ctl[2] is up; inject != 0 (test aid) raises it after the reset
+__global__ void nbody_ctl_reset_unless_aborted_kernel(int *ctl, int count, int inject) {
+    const bool aborted = ctl[2] != 0;
+    __syncthreads();
+    if (!aborted)
+        for (int i = threadIdx.x; i < count; i += blockDim.x) ctl[i] = (inject && i == 2) ? 1 : 0;
+}
+
 static int launch_seg(hgb_nbody *h, int variant, NbShard &s, const double *src, const PeerOut &out) {
     cudaStream_t st = s.dev->stream;
     if (!s.sym_ctl) {
         HGB_CUDA(cudaMalloc(&s.sym_ctl, sizeof(int) * kSymCtlInts));
+        HGB_CUDA(cudaMemsetAsync(s.sym_ctl, 0, sizeof(int) * kSymCtlInts, st));
         HGB_CUDA(cudaMalloc(&s.sym_ll, 48ull * h->npad));
         HGB_CUDA(cudaMemsetAsync(s.sym_ll, 0, 48ull * h->npad, st));   // tag 0 is never expected
     }
@@ -586,14 +598,20 @@ static int launch_seg(hgb_nbody *h, int variant, NbShard &s, const double *src, 
         HGB_CUDA(cudaMemsetAsync(s.seg_racc, 0, 48ull * h->npad, st));
     }
     HGB_TRY(seg_plan(h, s));
-    HGB_CUDA(cudaMemsetAsync(s.sym_ctl, 0, sizeof(int) * kSymCtlInts, st));
+    // Per-step reset of ticket, range flag and counters -- unless an earlier step of this advance gave a poll up
+    // (ctl[2]): then everything stays as that step left it, this step's workers see the flag and leave at once,
+    // and nb_advance reports the FIRST abandoned poll after the last step (it reads ctl only there).
+    nbody_ctl_reset_unless_aborted_kernel<<<1, kSymCtlInts, 0, st>>>(s.sym_ctl, kSymCtlInts,
+                                                                    h->seg_inject_abort == (int)h->seg_step ? 1 : 0);
+    HGB_LAUNCHED();
+    ++h->seg_step;
     s.sym_epoch = s.sym_epoch % 2047 + 1;
     SegArgs a;
     memset(&a, 0, sizeof a);
     a.src = src; a.npad = h->npad; a.n = h->n; a.T = (h->n + 63) / 64; a.seg = s.seg_plan_seg; a.tr = s.seg_plan_rows;
     a.tiles = s.seg_tiles; a.ntiles = s.seg_ntiles; a.ll = s.sym_ll; a.racc = s.seg_racc;
     a.epoch_tag = s.sym_epoch << 21; a.ctl = s.sym_ctl; a.spin_limit = kTriSpinLimit;
-    { const char *e = getenv("HGB_NBODY_SEG_HYST"); a.hyst = e ? atoi(e) : 0; }
+    a.hyst = h->seg_hyst;
     a.ll_down = a.ll; a.deal = a.T + 1; a.npeers = 1; a.ctl_all[0] = s.sym_ctl; a.range_slot = 1;   // one GPU: nothing leaves it
     const size_t smem = (size_t)kSymWarps * 6 * 3 * 32 * sizeof(double);
     const int grid = s.dev->sms * 2;
@@ -675,6 +693,8 @@ static void sym_defaults(hgb_nbody *h) {
     h->sym = g_default_sym;
     h->sym_auto = g_default_sym_auto ? 2 : 0;
     h->sym_min_n = g_default_sym_min_n;
+    if (const char *e = getenv("HGB_NBODY_SEG_HYST")) h->seg_hyst = atoi(e);
+    if (const char *e = getenv("HGB_NBODY_SEG_INJECT_ABORT")) h->seg_inject_abort = atoi(e);
 }
 
 extern "C" {
@@ -1030,6 +1050,7 @@ static int nb_advance(hgb_nbody *h, int iterations, float *ms, bool dyn) {
         int c[32] = {0};
         HGB_CUDA(cudaMemcpy(c, s0.sym_ctl, sizeof c, cudaMemcpyDeviceToHost));
         if (c[2]) {
+            HGB_CUDA(cudaMemset(s0.sym_ctl + 2, 0, 2 * sizeof(int)));   // reported: the handle can be uploaded to and stepped again
             set_error("segmented pair-symmetric wavefront abandoned: a hand-off did not arrive within the spin limit; %d tickets of %d items, "
                       "wanted tag epoch %u id %d, found tag %#x, chain word %d, row-sum word %d", c[0], s0.seg_ntiles * s0.seg_plan_rows,
                       (unsigned)c[6] >> 21, c[6] & 0x1fffff, (unsigned)c[7], c[25], c[26]);

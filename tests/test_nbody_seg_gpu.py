@@ -150,3 +150,26 @@ def test_seg_blocks_dealt_over_gpus_are_bit_identical(hgb, monkeypatch, n, iters
         for variant, rows, deal in ((6242, 0, 0), (6242, 1, 1), (4242, 2, 6), (7242, 3, 3)):
             cur, prev = seg_step(hgb, pos, iters, variant, seg=seg, rows=rows, weight=max(1, rows), want_prev=True, ngpus=g, deal=deal)
             assert np.array_equal(cur, one_cur) and np.array_equal(prev, one_prev), (g, variant, rows, deal)
+
+
+def test_seg_abandoned_step_is_reported_even_when_more_steps_follow(hgb, monkeypatch):
+    """A hand-off that never arrives makes the kernel give up and raise its abort flag; the host reads the flag
+    once, after the LAST step of an advance.  The flag therefore has to survive the per-step reset of the control
+    words of the steps in between (it did not: a full memset before every step erased it and the run returned
+    HGB_OK on garbage).  HGB_NBODY_SEG_INJECT_ABORT=k (read when the handle is made) raises the flag before
+    one-GPU segmented step k, which is how a lost hand-off looks to everything downstream."""
+    n = 3000
+    pos = synth.plummer(n, seed=11)
+    monkeypatch.setenv("HGB_NBODY_SEG_INJECT_ABORT", "0")
+    with hgb.nbody.NBody(n) as nb:
+        monkeypatch.delenv("HGB_NBODY_SEG_INJECT_ABORT")
+        nb.symmetric(6242, 0).upload(pos)
+        with pytest.raises(hgb.HgbError) as e:
+            nb.step(3)                                  # abandoned in step 0, two more steps after it
+        assert e.value.code == hgb._abi.HGB_ERR_STATE and "abandoned" in str(e.value)
+        # reported once; the same handle then works again (the injection was for step 0 only)
+        nb.upload(pos)
+        nb.step(2)
+        got = nb.download()
+    want, _ = oracle_run(pos, 2)
+    assert np.array_equal(got, want)
