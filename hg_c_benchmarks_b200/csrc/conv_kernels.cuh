@@ -558,6 +558,9 @@ conv_pad_columns_kernel(double *__restrict__ img, BandGeom g, int r0, int r1) {
 // FAST mode guard: is every inner pixel of rows [r0, r1) an integer-valued double?  (north_star: integer
 // images must stay bit-exact, so they keep the exact kernels even when FAST is requested.)  flag[0] is
 // set to 1 by any thread that finds a non-integer (or non-finite) pixel.
+// Only the W inner pixels of each row are looked at.  The caller's pad columns (read by the first iteration,
+// rewritten by every iteration) are left out on purpose: missing a non-integer value there can only keep the
+// EXACT kernels where FAST would have been allowed -- the error is on the bit-identical side.
 __global__ void __launch_bounds__(256)
 conv_not_integer_kernel(const double *__restrict__ img, BandGeom g, int r0, int r1, int *flag) {
     const int x = blockIdx.x * blockDim.x + threadIdx.x;

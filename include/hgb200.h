@@ -99,19 +99,22 @@ int hgb_nbody_tune(hgb_nbody *h, int block, int unroll, int warps);
  * from min_n up on one GPU; hgb_nbody_tune with a non-zero argument switches the pair-symmetric kernels off.
  * Variants 3000 + C (3002 default; 3010 + C with span counters): csrc/nbody_crow.cuh, a CTA of four warps per row.
  * Variants 4242 / 6242 (5242 / 7242 with span counters): csrc/nbody_seg.cuh, the first generation's warp on the segmented
- * schedule, plain / with software-pipelined groups (one GPU). */
+ * schedule, plain / with software-pipelined groups (the one-GPU default from n = 655 360; on request also dealt over
+ * several GPUs in blocks of 64 targets).  The thresholds live in auto_variant() (csrc/hgb_nbody.cu). */
 int hgb_nbody_set_symmetric(hgb_nbody *h, int variant, int min_n);
 /* Variants 2000 + C (C = 1..3 CTAs per SM; 2 = 2002; 2010 + C: with clock64 span counters) select the
  * second-generation pair-symmetric kernel (csrc/nbody_tri.cuh): forces evaluated per 32 x 8 minitile, the
  * ordered accumulation decoupled from them (row pass in registers, column pass through a shared-memory
  * transpose), rows cut into segments.  hgb_nbody_set_segment tunes its schedule: `seg` sources per item
  * (multiple of 32), `rows_per_tile` rows whose items are handed out together, `order_weight` of the segment
- * index in the ticket order (0 = default each: 8192, 16, 16).  It also runs on single-process multi-GPU
+ * index in the ticket order.  0 = the measured default of the kernel in effect, from tri_params() in
+ * csrc/hgb_nbody.cu: seg 16384 (8192 for cooperative rows on one GPU); rows per tile, one GPU / several: 8 / 16
+ * (nbody_tri), 1 / 8 (nbody_crow), 4 / 4 (nbody_seg); weight 32 / 64, 128 / 32, 64 / 64.  It also runs on single-process multi-GPU
  * handles with HGB_EXCHANGE_P2P: tile-rows of targets are dealt over the GPUs, the chain words cross NVLink
  * as tagged stores, the last row broadcasts the finished sums (no position exchange). */
 int hgb_nbody_set_segment(hgb_nbody *h, int seg, int rows_per_tile, int order_weight);
 /* Rows of targets per turn of a GPU when the pair-symmetric wavefront is dealt over several GPUs (rounded to a
- * multiple of rows_per_tile; 0 = default 16): rows I with I / rows_per_turn = t (mod GPUs) run on GPU t, so the
+ * multiple of rows_per_tile; 0 = default: 16 for nbody_tri, 8 for nbody_crow / nbody_seg): rows I with I / rows_per_turn = t (mod GPUs) run on GPU t, so the
  * chain words (reference src/nbody/nbody-run.c:19-21: the running sums of accel()) cross NVLink once per turn. */
 int hgb_nbody_set_deal(hgb_nbody *h, int rows_per_turn);
 /* the variant hgb_nbody_step will use on this handle as configured now (0: the standard kernel) */
@@ -186,7 +189,7 @@ int hgb_selftest_inv_sqrt(unsigned long long count, unsigned long long seed,
 #define HGB_CONV_EXACT 0 /* bit-identical to the reference: one multiply and one add per tap, row-major tap order */
 #define HGB_CONV_FAST 1  /* one fused multiply-add per tap (same order): floating-point images only, <= 1e-12
                           * relative to the reference after 10 iterations, not bit-identical; an image whose
-                          * pixels are all integer-valued keeps the EXACT kernels (it is classified at upload) */
+                          * inner pixels are all integer-valued keeps the EXACT kernels (classified at upload; pad columns are not looked at) */
 
 /* ---- convolution: drop-in --------------------------------------------- */
 /*
