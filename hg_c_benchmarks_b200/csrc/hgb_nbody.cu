@@ -182,7 +182,7 @@ constexpr int kTriMinNPerGpu = 131072;
 // Automatic choice (HGB_NBODY_SYM unset or 1), measured on B200 (profiles/r3g_small_n.txt, r3c_*, r2j_*).  What
 // decides is the number of bodies per GPU: it sets how long the wavefronts' serial chains are against the work.
 //   one GPU:   n < 49 152 standard kernel | < 229 376 cooperative rows (nbody_crow_kernel: +19 % at 64k, +31 % at 96k)
-//              | < 786 432 one warp per row (nbody_tri_kernel: +33 % at 384k, 374 vs 405 ms at 512k)
+//              | < 655 360 one warp per row (nbody_tri_kernel: +33 % at 384k, 374 vs 405 ms at 512k)
 //              | else the first generation's systolic warp on the segmented schedule, groups software-pipelined
 //                (nbody_seg_kernel: 1364 ms at 2^20 against 1410 for nbody_sym_kernel and 1440 for nbody_tri_kernel; 789 vs 830 at 786 432)
 //   g GPUs:    n / g < 65 536 standard kernel with ncclAllGather | < 262 144 cooperative rows | else one warp per row
@@ -443,7 +443,9 @@ static int launch_tri_step(hgb_nbody *h, int variant, int cur, int nxt) {
         HGB_CUDA(cudaSetDevice(s.dev->device));
         HGB_CUDA(cudaMemsetAsync(s.tri_ctl, 0, sizeof(int), s.dev->stream));                           // ticket
         HGB_CUDA(cudaMemsetAsync(s.tri_ctl + 4 + (parity ^ 1), 0, sizeof(int), s.dev->stream));        // next step's range flag
-        HGB_CUDA(cudaMemsetAsync(s.tri_ctl + 8, 0, 12 * sizeof(int), s.dev->stream));                  // profiling counters
+        HGB_CUDA(cudaMemsetAsync(s.tri_ctl + kCtlSpans, 0, kCtlSpanInts * sizeof(int), s.dev->stream)); // profiling counters (all 7 that hgb_nbody_sym_counters reads)
+        if (seg_variant(variant) && (variant / 1000 == 5 || variant / 1000 == 7))   // 5242 / 7242 count polls too: per step, like the spans
+            HGB_CUDA(cudaMemsetAsync(s.tri_ctl + kCtlSegProf0, 0, kCtlSegProfInts * sizeof(int), s.dev->stream));
     }
     // Shards that SHARE a device (HGB_VIRTUAL_GPUS, tests on a one-GPU box) do join their streams between
     // steps: a shard's finish / redo / memset kernels (little shared memory) are not scheduled onto SMs
@@ -782,20 +784,21 @@ int hgb_nbody_sym_counters(hgb_nbody *h, unsigned long long *out7) {
     if (!ctl) { set_error("the pair-symmetric kernel has not run on this handle"); return HGB_ERR_STATE; }
     HGB_CUDA(cudaSetDevice(s.dev->device));
     HGB_CUDA(cudaStreamSynchronize(s.dev->stream));
-    HGB_CUDA(cudaMemcpy(out7, ctl + 8, 7 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    HGB_CUDA(cudaMemcpy(out7, ctl + kCtlSpans, 7 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
     if (getenv("HGB_NBODY_SYM_HIST") && ctl == s.sym_ctl && seg_variant(sym_variant_in_effect(h))) {
         unsigned long long polled[5] = {0};
-        HGB_CUDA(cudaMemcpy(polled, ctl + 24, sizeof polled, cudaMemcpyDeviceToHost));
+        HGB_CUDA(cudaMemcpy(polled, ctl + kCtlSegPolled, sizeof polled[0], cudaMemcpyDeviceToHost));
+        HGB_CUDA(cudaMemcpy(polled + 1, ctl + kCtlSegPolledQuarter, 4 * sizeof polled[0], cudaMemcpyDeviceToHost));
         fprintf(stderr, "seg: chunk opens that had to poll: %llu; by quarter of the blocks: %llu %llu %llu %llu\n", polled[0], polled[1], polled[2],
                 polled[3], polled[4]);
         unsigned long long ahead[8] = {0};
-        HGB_CUDA(cudaMemcpy(ahead, ctl + 40, sizeof ahead, cudaMemcpyDeviceToHost));
+        HGB_CUDA(cudaMemcpy(ahead, ctl + kCtlSegAhead, sizeof ahead, cudaMemcpyDeviceToHost));
         fprintf(stderr, "seg: chunks the block above has published when an item starts (0, 1, 2, 3, 4-7, 8-15, 16-31, 32+):");
         for (int e = 0; e < 8; ++e) fprintf(stderr, " %llu", ahead[e]);
         fprintf(stderr, "\n");
     } else if (getenv("HGB_NBODY_SYM_HIST") && ctl == s.sym_ctl) {   // diagnostic: wait cycles by eighth of the row x quarter of the workers
         unsigned long long hist[40];
-        HGB_CUDA(cudaMemcpy(hist, ctl + 24, sizeof hist, cudaMemcpyDeviceToHost));
+        HGB_CUDA(cudaMemcpy(hist, ctl + kCtlSymHist, sizeof hist, cudaMemcpyDeviceToHost));
         fprintf(stderr, "sym: chunks the predecessor is ahead at a chunk open (0, 1, 2, 3, 4-7, 8-15, 16-31, 32+):");
         for (int e = 0; e < 8; ++e) fprintf(stderr, " %llu", hist[32 + e]);
         fprintf(stderr, "\n");
@@ -1050,7 +1053,7 @@ static int nb_advance(hgb_nbody *h, int iterations, float *ms, bool dyn) {
         int c[32] = {0};
         HGB_CUDA(cudaMemcpy(c, s0.sym_ctl, sizeof c, cudaMemcpyDeviceToHost));
         if (c[2]) {
-            HGB_CUDA(cudaMemset(s0.sym_ctl + 2, 0, 2 * sizeof(int)));   // reported: the handle can be uploaded to and stepped again
+            HGB_CUDA(cudaMemset(s0.sym_ctl + kCtlAbort, 0, 2 * sizeof(int)));   // reported: the handle can be uploaded to and stepped again
             set_error("segmented pair-symmetric wavefront abandoned: a hand-off did not arrive within the spin limit; %d tickets of %d items, "
                       "wanted tag epoch %u id %d, found tag %#x, chain word %d, row-sum word %d", c[0], s0.seg_ntiles * s0.seg_plan_rows,
                       (unsigned)c[6] >> 21, c[6] & 0x1fffff, (unsigned)c[7], c[25], c[26]);

@@ -179,7 +179,7 @@ nbody_seg_kernel(const __grid_constant__ SegArgs a) {
                 if ((unsigned)(t.x >> 32) != (a.epoch_tag | (unsigned)w)) break;
                 ahead = kk + 1;
             }
-            atomicAdd(reinterpret_cast<unsigned long long *>(a.ctl + 40) + (ahead >= 32 ? 7 : ahead >= 16 ? 6 : ahead >= 8 ? 5 : ahead >= 4 ? 4 : ahead), 1ull);
+            atomicAdd(reinterpret_cast<unsigned long long *>(a.ctl + kCtlSegAhead) + (ahead >= 32 ? 7 : ahead >= 16 ? 6 : ahead >= 8 ? 5 : ahead >= 4 ? 4 : ahead), 1ull);
         }
         const int last_chunk_of_item = (j_stop - 1) / CH;
 
@@ -203,7 +203,7 @@ nbody_seg_kernel(const __grid_constant__ SegArgs a) {
             const long long a0 = now();
             if (pf_chunk != c) prefetch_chunk(c);
             if (lower && !__all_sync(FULL, ll_ok(pf_ax, want_tag) && ll_ok(pf_ay, want_tag) && ll_ok(pf_az, want_tag))) {
-                if (PROF) { ++n_polled; if (lane == 0) atomicAdd(reinterpret_cast<unsigned long long *>(a.ctl + 26) + min(3, 4 * w / a.T), 1ull); }
+                if (PROF) { ++n_polled; if (lane == 0) atomicAdd(reinterpret_cast<unsigned long long *>(a.ctl + kCtlSegPolledQuarter) + min(3, 4 * w / a.T), 1ull); }
                 // caught up with block w-1: fall a.hyst chunks behind first (a later chunk of the same segment that block
                 // w-1 streams, not one of its own), so that the next prefetches find their words
                 const int ahead = min(min(c + a.hyst, last_chunk_of_item), (w - 1) * R - 1);
@@ -457,9 +457,9 @@ nbody_seg_kernel(const __grid_constant__ SegArgs a) {
         if (PROF) { t_item += now() - it0; ++n_items; }
     }
     if (PROF && lane == 0) {
-        unsigned long long *cnt = reinterpret_cast<unsigned long long *>(a.ctl + 8);
+        unsigned long long *cnt = reinterpret_cast<unsigned long long *>(a.ctl + kCtlSpans);
         atomicAdd(cnt + 0, (unsigned long long)t_wait); atomicAdd(cnt + 1, (unsigned long long)t_racc);
-        atomicAdd(reinterpret_cast<unsigned long long *>(a.ctl + 24), (unsigned long long)n_polled);
+        atomicAdd(reinterpret_cast<unsigned long long *>(a.ctl + kCtlSegPolled), (unsigned long long)n_polled);
         atomicAdd(cnt + 2, (unsigned long long)t_item); atomicAdd(cnt + 3, (unsigned long long)t_fast);
         atomicAdd(cnt + 4, (unsigned long long)t_slow); atomicAdd(cnt + 5, (unsigned long long)n_items);
         atomicAdd(cnt + 6, (unsigned long long)n_chunks);

@@ -41,6 +41,22 @@
 namespace hgb {
 
 constexpr int kSymCtlInts = 128;   // ctl[0] = ticket counter, ctl[1] = range flag, ctl[8..21] profiling counters, ctl[24..] (PROF) wait cycles by position in the row x worker size class
+// Control words of the pair-symmetric kernels (sym_ctl: kSymCtlInts ints, tri_ctl: kTriCtlInts ints).  One owner per
+// slot; the host resets kCtlTicket, the range flag(s) and the profiling ranges per step and leaves the abort flag
+// and the abandoned-poll record alone until it has read them.
+constexpr int kCtlTicket = 0;        // next item / row to hand out
+constexpr int kCtlRange = 1;         // sym_ctl: an operand left the range of the packed words -> the step is redone
+constexpr int kCtlAbort = 2;         // a poll hit the spin limit: every worker gives up
+constexpr int kCtlAbortFirst = 3;    // latch: the first poll to give up fills the record below
+constexpr int kCtlRangeParity = 4;   // tri_ctl: range flag of even / odd steps (4, 5)
+constexpr int kCtlWantTag = 6;       // abandoned-poll record: tag waited for, tag found (7, 24), chain word (25), row word (26)
+constexpr int kCtlSpans = 8;         // 7 x u64 clock64 spans / counts of the profiling variants: ints 8..21
+constexpr int kCtlSpanInts = 14;
+constexpr int kCtlSymHist = 24;      // sym_ctl, first generation only (no abandoned-poll record there): 40 x u64 histogram
+constexpr int kCtlSegPolled = 34;    // segmented kernel, PROF: chunk opens that had to poll (u64: 34, 35)
+constexpr int kCtlSegAhead = 40;     // ... chunks the block above has published at an item start (8 x u64: 40..55)
+constexpr int kCtlSegPolledQuarter = 56;   // ... polled opens by quarter of the blocks (4 x u64: 56..63)
+constexpr int kCtlSegProf0 = 34, kCtlSegProfInts = 30;   // the segmented kernel's PROF range for the per-step reset
 
 // Hand-off words (the "LL" scheme of collective libraries): every 64-bit word carries 32 bits of
 // payload and a 32-bit tag, so a naturally aligned 8-byte store publishes data and flag together --
