@@ -119,7 +119,9 @@ static int launch_step(const hgb_nbody *h, const NbShard &s, const double *src, 
     HGB_VW(128, 1) HGB_VW(128, 2) HGB_VW(128, 4)
     HGB_V(128, 1, 28) HGB_V(128, 2, 28) HGB_V(128, 4, 28)   // 7 CTAs per SM: 1036 slots
     HGB_VW(256, 1) HGB_VW(256, 2) HGB_VW(256, 4)
-    HGB_V(64, 2, 28) HGB_V(64, 2, 24) HGB_V(64, 4, 24) HGB_V(64, 1, 28)   // small target counts
+#ifdef HGB_EXPERIMENTAL_VARIANTS
+    HGB_V(64, 2, 28) HGB_V(64, 2, 24) HGB_V(64, 4, 24) HGB_V(64, 1, 28)   // small target counts: measured the same or slower (profiles/r2a_nbody_small_sweep.txt)
+#endif
 #undef HGB_VW
 #undef HGB_V
     set_error("no nbody kernel variant block=%d unroll=%d warps=%d", block, unroll, warps);
@@ -135,14 +137,29 @@ constexpr int kSymDefaultMinN = 393216;                    // measured: slower t
 // third generation (nbody_crow.cuh, a CTA of W warps per row): 30PC (W = 4) / 31PC (W = 8), P = profiling, C = CTAs per SM
 static bool crow_variant(int v) {
     const int c = v % 10, p = v / 10 % 10, w = v / 100 % 10;   // p: 1 profiling, 2 row pass fused into the next force block, 3 both
+#ifdef HGB_EXPERIMENTAL_VARIANTS   // measured and rejected: row pass fused into the next force block (p >= 2: -20 %), W = 8 warps per row (w == 1)
     return v >= 3001 && v <= 3132 && p <= 3 && ((w == 0 && (c == 1 || c == 2)) || (w == 1 && c == 1 && p <= 1));
+#else
+    return v >= 3001 && v <= 3012 && p <= 1 && w == 0 && (c == 1 || c == 2);
+#endif
 }
 // second or third generation: 200C / 201C (profiling), or a cooperative-row variant (same buffers, plan and multi-GPU dealing)
 // 202C: row pass fused into the next minitile's force block (ROWPIPE)
-static bool tri_variant(int v) { return (v >= 2001 && v <= 2023 && (v % 10) >= 1 && (v % 10) <= 3) || crow_variant(v); }
+#ifdef HGB_EXPERIMENTAL_VARIANTS
+constexpr int kTriLastVariant = 2023;
+#else
+constexpr int kTriLastVariant = 2013;   // 202C (+0.3 %) is not built
+#endif
+static bool tri_variant(int v) { return (v >= 2001 && v <= kTriLastVariant && (v % 10) >= 1 && (v % 10) <= 3) || crow_variant(v); }
 
 // 4242 (5242 with span counters): the first generation's systolic warp (R = 2, U = 4, 2 CTAs per SM) on the segmented schedule
-static bool seg_variant(int v) { return v == 4242 || v == 5242 || v == 6242 || v == 7242 || v == 6241 || v == 7241 || v == 6223 || v == 6224; }   // ...1: one CTA per SM (diagnostic)   // 6242 / 7242: pipelined groups
+static bool seg_variant(int v) {   // 6242 / 7242: pipelined groups
+    if (v == 4242 || v == 5242 || v == 6242 || v == 7242) return true;
+#ifdef HGB_EXPERIMENTAL_VARIANTS       // measured and rejected: one CTA per SM (6241 / 7241, diagnostic), U = 2 with 3 / 4 CTAs per SM
+    if (v == 6241 || v == 7241 || v == 6223 || v == 6224) return true;
+#endif
+    return false;
+}
 
 static bool sym_variant_known(int v) {
     if (tri_variant(v) || seg_variant(v)) return true;
@@ -502,15 +519,18 @@ static int launch_tri_step(hgb_nbody *h, int variant, int cur, int nxt) {
                 case 3002: rc = launch_crow_variant<4, 2, false>(a, grid, s.dev->stream); break;
                 case 3011: rc = launch_crow_variant<4, 1, true>(a, grid, s.dev->stream); break;
                 case 3012: rc = launch_crow_variant<4, 2, true>(a, grid, s.dev->stream); break;
+#ifdef HGB_EXPERIMENTAL_VARIANTS
                 case 3021: rc = launch_crow_variant<4, 1, false, true>(a, grid, s.dev->stream); break;
                 case 3022: rc = launch_crow_variant<4, 2, false, true>(a, grid, s.dev->stream); break;
                 case 3031: rc = launch_crow_variant<4, 1, true, true>(a, grid, s.dev->stream); break;
                 case 3032: rc = launch_crow_variant<4, 2, true, true>(a, grid, s.dev->stream); break;
                 case 3101: rc = launch_crow_variant<8, 1, false>(a, grid, s.dev->stream); break;
                 case 3111: rc = launch_crow_variant<8, 1, true>(a, grid, s.dev->stream); break;
+#endif
                 default: set_error("no nbody_crow variant %d", variant);
             }
         } else
+#ifdef HGB_EXPERIMENTAL_VARIANTS
         if ((variant / 10) % 10 == 2) {
             switch (ctas) {
                 case 1: rc = launch_tri_variant<1, false, true>(a, grid, s.dev->stream); break;
@@ -519,6 +539,7 @@ static int launch_tri_step(hgb_nbody *h, int variant, int cur, int nxt) {
                 default: set_error("no nbody_tri variant %d", variant);
             }
         } else
+#endif
         switch (ctas * 2 + (prof ? 1 : 0)) {
             case 2: rc = launch_tri_variant<1, false>(a, grid, s.dev->stream); break;
             case 3: rc = launch_tri_variant<1, true>(a, grid, s.dev->stream); break;
@@ -617,11 +638,14 @@ static int launch_seg(hgb_nbody *h, int variant, NbShard &s, const double *src, 
     a.ll_down = a.ll; a.deal = a.T + 1; a.npeers = 1; a.ctl_all[0] = s.sym_ctl; a.range_slot = 1;   // one GPU: nothing leaves it
     const size_t smem = (size_t)kSymWarps * 6 * 3 * 32 * sizeof(double);
     const int grid = s.dev->sms * 2;
+#ifdef HGB_EXPERIMENTAL_VARIANTS
     if (variant == 6223) nbody_seg_kernel<2, 2, 3, false, true><<<s.dev->sms * 3, kSymWarps * 32, smem, st>>>(a);
     else if (variant == 6224) nbody_seg_kernel<2, 2, 4, false, true><<<s.dev->sms * 4, kSymWarps * 32, smem, st>>>(a);
     else if (variant == 6241) nbody_seg_kernel<2, 4, 1, false, true><<<s.dev->sms, kSymWarps * 32, smem, st>>>(a);
     else if (variant == 7241) nbody_seg_kernel<2, 4, 1, true, true><<<s.dev->sms, kSymWarps * 32, smem, st>>>(a);
-    else if (variant == 5242) nbody_seg_kernel<2, 4, 2, true><<<grid, kSymWarps * 32, smem, st>>>(a);
+    else
+#endif
+    if (variant == 5242) nbody_seg_kernel<2, 4, 2, true><<<grid, kSymWarps * 32, smem, st>>>(a);
     else if (variant == 6242) nbody_seg_kernel<2, 4, 2, false, true><<<grid, kSymWarps * 32, smem, st>>>(a);
     else if (variant == 7242) nbody_seg_kernel<2, 4, 2, true, true><<<grid, kSymWarps * 32, smem, st>>>(a);
     else nbody_seg_kernel<2, 4, 2, false><<<grid, kSymWarps * 32, smem, st>>>(a);
@@ -930,7 +954,11 @@ int hgb_nbody_config(hgb_nbody *h, int mode, int exchange) {
 
 int hgb_nbody_tune(hgb_nbody *h, int block, int unroll, int warps) {
     HGB_ARG(h, "handle");
+#ifdef HGB_EXPERIMENTAL_VARIANTS
     HGB_ARG(block == 0 || block == 64 || block == 128 || block == 256, "block in {64,128,256}");
+#else
+    HGB_ARG(block == 0 || block == 128 || block == 256, "block in {128,256} (64-thread CTAs: build with -DHGB_EXPERIMENTAL_VARIANTS)");
+#endif
     HGB_ARG(unroll == 0 || unroll == 1 || unroll == 2 || unroll == 4, "unroll in {1,2,4}");
     HGB_ARG(warps == 0 || warps == 24 || warps == 28 || warps == 32 || warps == 40, "warps in {24,28,32,40}");
     HGB_ARG(warps != 28 || block != 256, "warps = 28 needs 64- or 128-thread CTAs");

@@ -13,7 +13,7 @@ from hg_c_benchmarks_b200 import synth
 
 pytestmark = [pytest.mark.gpu]
 
-VARIANTS = [3001, 3002, 3011, 3012, 3101, 3111, 3021, 3022, 3031, 3032]
+VARIANTS = [3001, 3002, 3011, 3012]   # W = 8 (31xx) and the fused row pass (302x / 303x) measured slower: experimental builds only
 
 
 def sha(a):
@@ -40,7 +40,7 @@ def oracle_run(pos, iters):
 @pytest.mark.parametrize("n,iters,seg", [(1, 2, 32), (3, 10, 0), (31, 2, 32), (32, 1, 32), (33, 2, 32), (65, 2, 64),
                                          (129, 3, 96), (200, 2, 64), (1023, 2, 32), (1025, 2, 0), (2000, 1, 160),
                                          (4097, 3, 512), (9000, 1, 1024), (9000, 2, 0)])
-@pytest.mark.parametrize("variant", [3002, 3101, 3022])
+@pytest.mark.parametrize("variant", [3002, 3001, 3012])
 def test_crow_ragged_sizes_vs_oracle(hgb, variant, n, iters, seg):
     pos = synth.uniform_cube(n, seed=n)
     want_cur, want_prev = oracle_run(pos, iters)
@@ -155,7 +155,7 @@ def test_crow_64k_plummer_all_bodies_equal_the_standard_kernel(hgb):
         std = nb.download()
     assert np.array_equal(crow_step(hgb, pos, 1)[targets], want)
     assert np.array_equal(crow_step(hgb, pos, 2), std)
-    assert np.array_equal(crow_step(hgb, pos, 2, 3101), std)
+    assert np.array_equal(crow_step(hgb, pos, 2, 3001), std)
 
 
 def test_crow_full_size_1m_all_bodies_equal_the_standard_kernel(hgb):

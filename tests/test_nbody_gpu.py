@@ -82,7 +82,7 @@ def test_every_kernel_variant_gives_the_same_bits(hgb):
     want = np.zeros_like(pos)
     port.nbody_step_range(pos, want, 0, n)
     shapes = [(b, u, w) for b in (128, 256) for u in (1, 2, 4) for w in (24, 32, 40)]
-    shapes += [(128, 2, 28), (64, 2, 28), (64, 2, 24), (64, 4, 24), (64, 1, 28)]   # 64: small target counts
+    shapes += [(128, 2, 28)]   # 64-thread CTAs measured no faster: built only with -DHGB_EXPERIMENTAL_VARIANTS
     for block, unroll, warps in shapes:
         with hgb.nbody.NBody(n) as nb:
             nb.tune(block, unroll, warps).upload(pos)

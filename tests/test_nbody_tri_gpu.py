@@ -46,7 +46,7 @@ def test_tri_ragged_sizes_vs_oracle(hgb, n, iters, seg):
     assert np.array_equal(cur, want_cur) and np.array_equal(prev, want_prev)
 
 
-@pytest.mark.parametrize("variant", [2001, 2002, 2003, 2011, 2012, 2013, 2021, 2022, 2023])
+@pytest.mark.parametrize("variant", [2001, 2002, 2003, 2011, 2012, 2013])   # 202x (fused row pass, +0.3 %): experimental builds only
 @pytest.mark.parametrize("seg,rows,weight", [(64, 1, 1), (64, 3, 2), (2048, 16, 16), (96, 256, 1), (0, 0, 0)])
 def test_tri_every_variant_and_schedule_gives_the_same_bits(hgb, variant, seg, rows, weight):
     from oracle import port
