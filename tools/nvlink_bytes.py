@@ -41,7 +41,31 @@ def counters():
         m = re.search(r"Data Rx: (\d+) KiB", line)
         if m and gpu is not None:
             res[gpu][1] += int(m.group(1))
+    if "N/A" in out and not any(a or b for a, b in res.values()):
+        nv = nvml_counters()
+        if nv:
+            return nv, out
+        return {}, out
     return res, out
+
+
+def nvml_counters():
+    """the same counters through NVML field values (KiB, all links of a GPU summed: scope id 0xffffffff), or {}"""
+    try:
+        import pynvml as nv
+        nv.nvmlInit()
+        res = {}
+        for i in range(nv.nvmlDeviceGetCount()):
+            h = nv.nvmlDeviceGetHandleByIndex(i)
+            vals = nv.nvmlDeviceGetFieldValues(h, [(nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, 0xffffffff),
+                                                   (nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX, 0xffffffff)])
+            if any(v.nvmlReturn != 0 for v in vals):
+                return {}
+            res[i] = [int(vals[0].value.ullVal), int(vals[1].value.ullVal)]
+        return res
+    except Exception as e:   # noqa: BLE001 -- a diagnostic tool: say why and go on with the plan numbers
+        print(f"NVML field values unavailable: {e!r}")
+        return {}
 
 
 pos = synth.uniform_cube(n, seed=1)
@@ -56,8 +80,8 @@ with H.nbody.NBody(n, ngpus=g, exchange=H._abi.EXCHANGE_P2P) as nb:
     after, _ = counters()
 print(f"n={n} g={g} steps={steps} {ms:.2f} ms/step  [{what}]")
 if not before:
-    print("no NVLink counters on this box:\n" + raw[:600])
-    sys.exit(0)
+    print("the driver exposes no NVLink data counters on this box (nvidia-smi nvlink -gt d below; NVML field values likewise):\n" + raw[:300])
+    after = {}
 # rows per turn as tri_default_deal() has them (no hgb_nbody_set_deal here); rows of 64 targets for the segmented kernel
 kernel = what[0]
 deal = 16 if "nbody_tri" in kernel else 8 if ("nbody_crow" in kernel or "nbody_seg" in kernel) else None
